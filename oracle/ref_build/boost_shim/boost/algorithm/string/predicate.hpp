@@ -1,0 +1,2 @@
+#pragma once
+#include <boost/algorithm/string.hpp>
