@@ -1,0 +1,161 @@
+// TEST INFRASTRUCTURE / reference-side tool. Drives the UNMODIFIED reference (Cantera 4.0.0a2
+// built by build_ref.sh) on seeded synthetic states and dumps inputs + reference outputs as a
+// named-array file (ctb_arrays.h) for tests/golden/.
+//
+//   gen_golden rates  <yaml> <phase> <out> <N> <seed>
+//   gen_golden ddx    <yaml> <phase> <out> <N> <seed>
+//   gen_golden rhs    <yaml> <phase> <out> <N> <seed>
+//   gen_golden ignite <yaml> <phase> <out> <N> <seed> <fuel> <nO2> <O2> <N2> <Tlo> <Thi> <Plo_atm> <Phi_atm> <tEnd> [rtol atol]
+//
+// States follow SURVEY.md §8(d): T ~ U(800, 2500) K, P = 101325 * U(1, 50) Pa, Y_k = u_k / sum u.
+#include "ctb_arrays.h"
+
+#include "cantera/base/Solution.h"
+#include "cantera/base/global.h"
+#include "cantera/kinetics/Kinetics.h"
+#include "cantera/thermo/ThermoPhase.h"
+#include "cantera/zeroD/IdealGasConstPressureMoleReactor.h"
+#include "cantera/zeroD/ReactorNet.h"
+#include "cantera/numerics/eigen_sparse.h"
+
+#include <cmath>
+#include <iostream>
+#include <random>
+
+using namespace Cantera;
+
+struct States {
+    std::vector<double> T, P, Y;
+};
+
+static States randomStates(size_t N, size_t K, uint64_t seed)
+{
+    std::mt19937_64 rng(seed);
+    std::uniform_real_distribution<double> U(0.0, 1.0);
+    States s;
+    s.T.resize(N); s.P.resize(N); s.Y.resize(N * K);
+    for (size_t n = 0; n < N; n++) {
+        s.T[n] = 800.0 + 1700.0 * U(rng);
+        s.P[n] = OneAtm * (1.0 + 49.0 * U(rng));
+        double sum = 0;
+        for (size_t k = 0; k < K; k++) {
+            s.Y[n * K + k] = U(rng);
+            sum += s.Y[n * K + k];
+        }
+        for (size_t k = 0; k < K; k++) {
+            s.Y[n * K + k] /= sum;
+        }
+    }
+    // edge cases the reference defines behaviour for: a negative mass fraction is clipped
+    // (Phase.cpp:342-360), exact zeros, an un-normalised vector, T exactly at a NASA Tmid.
+    if (N >= 8) {
+        s.Y[0 * K + 0] = -1e-3;
+        for (size_t k = 1; k < K; k += 2) s.Y[1 * K + k] = 0.0;
+        for (size_t k = 0; k < K; k++) s.Y[2 * K + k] *= 3.0;
+        s.T[3] = 1000.0;
+        for (size_t k = 0; k < K; k++) s.Y[4 * K + k] = (k == K - 1) ? 1.0 : 0.0;
+    }
+    return s;
+}
+
+static void densify(const Eigen::SparseMatrix<double>& J, double* out, size_t K)
+{
+    for (size_t i = 0; i < K * K; i++) out[i] = 0.0;
+    for (int c = 0; c < J.outerSize(); c++) {
+        for (Eigen::SparseMatrix<double>::InnerIterator it(J, c); it; ++it) {
+            out[(size_t) it.col() * K + it.row()] = it.value();
+        }
+    }
+}
+
+static int runRates(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    auto kin = sol->kinetics();
+    size_t K = gas->nSpecies(), R = kin->nReactions();
+    States s = randomStates(N, K, seed);
+    std::vector<double> kf(N * R), kc(N * R), ropf(N * R), ropr(N * R), ropn(N * R);
+    std::vector<double> wdot(N * K), cdot(N * K), ddot(N * K);
+    for (size_t n = 0; n < N; n++) {
+        gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+        kin->getFwdRateConstants(span<double>(&kf[n * R], R));
+        kin->getEquilibriumConstants(span<double>(&kc[n * R], R));
+        kin->getFwdRatesOfProgress(span<double>(&ropf[n * R], R));
+        kin->getRevRatesOfProgress(span<double>(&ropr[n * R], R));
+        kin->getNetRatesOfProgress(span<double>(&ropn[n * R], R));
+        kin->getNetProductionRates(span<double>(&wdot[n * K], K));
+        kin->getCreationRates(span<double>(&cdot[n * K], K));
+        kin->getDestructionRates(span<double>(&ddot[n * K], K));
+    }
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) R});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    f.add("kf", kf); f.add("kc", kc); f.add("ropf", ropf); f.add("ropr", ropr); f.add("ropnet", ropn);
+    f.add("wdot", wdot); f.add("cdot", cdot); f.add("ddot", ddot);
+    f.save(out);
+    return 0;
+}
+
+static int runDdx(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    auto kin = sol->kinetics();
+    size_t K = gas->nSpecies();
+    States s = randomStates(N, K, seed);
+    // variants: default, skip-falloff, skip-third-bodies, rtol-delta 1e-6, and ddCi default
+    std::vector<double> jdef(N * K * K), jsf(N * K * K), jstb(N * K * K), jdel(N * K * K), jci(N * K * K);
+    for (size_t n = 0; n < N; n++) {
+        gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+        AnyMap st;
+        kin->setDerivativeSettings(st); // empty map = reset to defaults
+        densify(kin->netProductionRates_ddX(), &jdef[n * K * K], K);
+        densify(kin->netProductionRates_ddCi(), &jci[n * K * K], K);
+        st["skip-falloff"] = true;
+        kin->setDerivativeSettings(st);
+        densify(kin->netProductionRates_ddX(), &jsf[n * K * K], K);
+        AnyMap st2;
+        kin->setDerivativeSettings(st2);
+        st2["skip-third-bodies"] = true;
+        kin->setDerivativeSettings(st2);
+        densify(kin->netProductionRates_ddX(), &jstb[n * K * K], K);
+        AnyMap st3;
+        kin->setDerivativeSettings(st3);
+        st3["rtol-delta"] = 1e-6;
+        kin->setDerivativeSettings(st3);
+        densify(kin->netProductionRates_ddX(), &jdel[n * K * K], K);
+        AnyMap st4;
+        kin->setDerivativeSettings(st4);
+    }
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) kin->nReactions()});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    f.add("ddX", jdef); f.add("ddX_skip_falloff", jsf); f.add("ddX_skip_third_bodies", jstb);
+    f.add("ddX_delta1e-6", jdel); f.add("ddCi", jci);
+    f.save(out);
+    return 0;
+}
+
+static int runRhs(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    size_t K = gas->nSpecies();
+    States s = randomStates(N, K, seed);
+    auto reactor = std::make_shared<IdealGasConstPressureMoleReactor>(sol, false);
+    ReactorNet net(reactor);
+    std::vector<double> y(N * (K + 1)), ydot(N * (K + 1));
+    for (size_t n = 0; n < N; n++) {
+        for (size_t k = 0; k < K; k++) s.Y[n * K + k] = std::abs(s.Y[n * K + k]);
+        gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+        net.setInitialTime(0.0);
+        net.initialize();
+        net.getState(span<double>(&y[n * (K + 1)], K + 1));
+        net.eval(0.0, span<double>(&y[n * (K + 1)], K + 1), span<double>(&ydot[n * (K + 1)], K + 1),
+                 span<double>());
+    }
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) sol->kinetics()->nReactions()});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    f.add("y", y); f.add("ydot", ydot);
+    f.save(out);
+    return 0;
+}
