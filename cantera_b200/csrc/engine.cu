@@ -1,0 +1,260 @@
+// engine.cu — BatchedGasKinetics host side: table upload, host<->device staging, launches.
+#include "engine.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace ctb {
+
+void cudaCheck(cudaError_t e, const char* where)
+{
+    if (e != cudaSuccess) {
+        throw CtbError(where, std::string("CUDA error: ") + cudaGetErrorString(e));
+    }
+}
+
+void DevBuf::reserve(size_t n)
+{
+    if (n <= bytes) return;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    cudaCheck(cudaMalloc(&p, n), "DevBuf::reserve");
+    bytes = n;
+}
+
+DevBuf::~DevBuf()
+{
+    if (p) cudaFree(p);
+}
+
+BatchedGasKinetics::BatchedGasKinetics(const ctb_mech_tables& tables, int device)
+    : m_tables(cantera_b200::MechTables::fromView(tables))
+{
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        // There is deliberately no CPU fallback.
+        throw CtbError("BatchedGasKinetics", std::string("no usable CUDA device (")
+                       + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0")
+                       + "); this engine has no CPU path");
+    }
+    if (device < 0 || device >= ndev) {
+        throw CtbError("BatchedGasKinetics", "device index " + std::to_string(device) + " out of range");
+    }
+    cudaCheck(cudaSetDevice(device), "cudaSetDevice");
+    cudaDeviceProp prop;
+    cudaCheck(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    if (prop.major < 10) {
+        throw CtbError("BatchedGasKinetics", "built for sm_100a (Blackwell); device is sm_"
+                       + std::to_string(prop.major) + std::to_string(prop.minor));
+    }
+    if (m_tables.n_species < 1) throw CtbError("BatchedGasKinetics", "mechanism has no species");
+    try {
+        m_packed = packMechanism(m_tables.view());
+    } catch (std::exception& ex) {
+        throw CtbError("BatchedGasKinetics", ex.what());
+    }
+    m_dev.view = m_packed.v;
+    m_dev.device = device;
+    m_dev.numSMs = prop.multiProcessorCount;
+    cudaCheck(cudaDeviceGetAttribute(&m_dev.smemOptIn, cudaDevAttrMaxSharedMemoryPerBlockOptin, device),
+              "cudaDeviceGetAttribute");
+    cudaCheck(cudaMalloc((void**) &m_dev.dBlob, m_packed.blob.size()), "cudaMalloc(mechanism)");
+    cudaCheck(cudaMemcpy(m_dev.dBlob, m_packed.blob.data(), m_packed.blob.size(), cudaMemcpyHostToDevice),
+              "cudaMemcpy(mechanism)");
+    cudaCheck(cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    for (int i = 0; i < 2; i++) {
+        cudaCheck(cudaStreamCreateWithFlags(&m_copyStream[i], cudaStreamNonBlocking), "cudaStreamCreate");
+        cudaCheck(cudaEventCreateWithFlags(&m_evt[i], cudaEventDisableTiming), "cudaEventCreate");
+    }
+}
+
+BatchedGasKinetics::~BatchedGasKinetics()
+{
+    cudaSetDevice(m_dev.device);
+    if (m_dev.dBlob) cudaFree(m_dev.dBlob);
+    for (int i = 0; i < 2; i++) {
+        if (m_copyStream[i]) cudaStreamDestroy(m_copyStream[i]);
+        if (m_evt[i]) cudaEventDestroy(m_evt[i]);
+    }
+    if (m_stream) cudaStreamDestroy(m_stream);
+}
+
+void BatchedGasKinetics::uploadMultipliers()
+{
+    const int R = nReactions();
+    double* dst = reinterpret_cast<double*>(m_packed.blob.data() + m_packed.v.o_mult);
+    for (int e = 0; e < R; e++) dst[e] = m_tables.multiplier[m_packed.perm[e]];
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    cudaCheck(cudaMemcpy(m_dev.dBlob + m_packed.v.o_mult, dst, sizeof(double) * R, cudaMemcpyHostToDevice),
+              "cudaMemcpy(multipliers)");
+}
+
+void BatchedGasKinetics::setMultiplier(int i, double f)
+{
+    if (i < 0 || i >= nReactions()) {
+        throw CtbError("BatchedGasKinetics::setMultiplier", "reaction index " + std::to_string(i)
+                       + " out of range (nReactions = " + std::to_string(nReactions()) + ")");
+    }
+    synchronize();
+    m_tables.multiplier[i] = f;
+    uploadMultipliers();
+}
+
+double BatchedGasKinetics::multiplier(int i) const
+{
+    if (i < 0 || i >= nReactions()) {
+        throw CtbError("BatchedGasKinetics::multiplier", "reaction index " + std::to_string(i) + " out of range");
+    }
+    return m_tables.multiplier[i];
+}
+
+void BatchedGasKinetics::setDerivativeSettings(bool skipThirdBodies, bool skipFalloff, double rtolDelta)
+{
+    if (!(rtolDelta > 0.0)) {
+        throw CtbError("BatchedGasKinetics::setDerivativeSettings", "rtol-delta must be positive");
+    }
+    m_skip3b = skipThirdBodies;
+    m_skipFalloff = skipFalloff;
+    m_rtolDelta = rtolDelta; // kept for API symmetry: the falloff [M]-derivative is analytic here
+}
+
+void BatchedGasKinetics::synchronize()
+{
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    cudaCheck(cudaStreamSynchronize(stream()), "cudaStreamSynchronize");
+}
+
+static bool anyFull(const RateOutputs& o)
+{
+    return o.cdot || o.ddot || o.ropf || o.ropr || o.ropnet || o.kf || o.kc;
+}
+
+void BatchedGasKinetics::rates(long long N, const double* T, const double* P, const double* Y,
+                               long long ldY, const RateOutputs& out, int memspace)
+{
+    const int K = nSpecies(), R = nReactions();
+    if (N < 0) throw CtbError("BatchedGasKinetics::rates", "negative number of states");
+    if (N == 0) return;
+    if (!T || !P || !Y) throw CtbError("BatchedGasKinetics::rates", "null state pointer");
+    if (ldY < K) throw CtbError("BatchedGasKinetics::rates", "ldY = " + std::to_string(ldY)
+                                + " is smaller than the number of species " + std::to_string(K));
+    const bool wantW = out.wdot || out.cdot || out.ddot;
+    const bool wantR = out.ropf || out.ropr || out.ropnet || out.kf || out.kc;
+    if (!wantW && !wantR) throw CtbError("BatchedGasKinetics::rates", "no output requested");
+    if (wantW && out.ldW < K) throw CtbError("BatchedGasKinetics::rates", "ldW is smaller than the number of species");
+    if (wantR && out.ldR < R) throw CtbError("BatchedGasKinetics::rates", "ldR is smaller than the number of reactions");
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    const bool full = anyFull(out);
+
+    if (memspace == CTB_DEVICE) {
+        RatesArgs a = {N, T, P, Y, ldY, out.wdot, out.cdot, out.ddot, out.ldW,
+                       out.ropf, out.ropr, out.ropnet, out.kf, out.kc, out.ldR};
+        launchRates(m_dev, a, full, stream());
+        cudaCheck(cudaGetLastError(), "ratesKernel launch");
+        return;
+    }
+    if (memspace != CTB_HOST) throw CtbError("BatchedGasKinetics::rates", "memspace must be CTB_HOST or CTB_DEVICE");
+
+    // Host buffers: chunks double-buffered over two streams so that the copies of one chunk
+    // overlap the kernel of the other.
+    double* outsW[3] = {out.wdot, out.cdot, out.ddot};
+    double* outsR[5] = {out.ropf, out.ropr, out.ropnet, out.kf, out.kc};
+    int nW = 0, nR = 0;
+    for (double* p : outsW) nW += p != nullptr;
+    for (double* p : outsR) nR += p != nullptr;
+    const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) nW * K + (size_t) nR * R);
+    long long chunk = std::max<long long>(1024, std::min<long long>(N, (long long) ((256u << 20) / perState)));
+    chunk = std::min<long long>(chunk, std::max<long long>(1024, (N + 3) / 4));
+    for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
+    int b = 0;
+    for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
+        const long long n = std::min(chunk, N - n0);
+        cudaStream_t st = m_copyStream[b];
+        double* d = m_stage[b].as<double>();
+        double* dT = d; d += chunk;
+        double* dP = d; d += chunk;
+        double* dY = d; d += chunk * K;
+        cudaCheck(cudaMemcpyAsync(dT, T + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D T");
+        cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
+        cudaCheck(cudaMemcpy2DAsync(dY, sizeof(double) * K, Y + n0 * ldY, sizeof(double) * ldY,
+                                    sizeof(double) * K, n, cudaMemcpyHostToDevice, st), "H2D Y");
+        RatesArgs a = {};
+        a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.ldW = K; a.ldR = R;
+        double** slotsW[3] = {&a.wdot, &a.cdot, &a.ddot};
+        double** slotsR[5] = {&a.ropf, &a.ropr, &a.ropnet, &a.kf, &a.kc};
+        for (int i = 0; i < 3; i++) if (outsW[i]) { *slotsW[i] = d; d += chunk * K; }
+        for (int i = 0; i < 5; i++) if (outsR[i]) { *slotsR[i] = d; d += chunk * R; }
+        launchRates(m_dev, a, full, st);
+        cudaCheck(cudaGetLastError(), "ratesKernel launch");
+        for (int i = 0; i < 3; i++) {
+            if (outsW[i]) {
+                cudaCheck(cudaMemcpy2DAsync(outsW[i] + n0 * out.ldW, sizeof(double) * out.ldW, *slotsW[i],
+                                            sizeof(double) * K, sizeof(double) * K, n, cudaMemcpyDeviceToHost, st),
+                          "D2H");
+            }
+        }
+        for (int i = 0; i < 5; i++) {
+            if (outsR[i]) {
+                cudaCheck(cudaMemcpy2DAsync(outsR[i] + n0 * out.ldR, sizeof(double) * out.ldR, *slotsR[i],
+                                            sizeof(double) * R, sizeof(double) * R, n, cudaMemcpyDeviceToHost, st),
+                          "D2H");
+            }
+        }
+    }
+    cudaCheck(cudaStreamSynchronize(m_copyStream[0]), "cudaStreamSynchronize");
+    cudaCheck(cudaStreamSynchronize(m_copyStream[1]), "cudaStreamSynchronize");
+}
+
+void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P, const double* Y,
+                                  long long ldY, double* jac, long long bufLen, bool ddCi, int memspace)
+{
+    const int K = nSpecies();
+    if (N < 0) throw CtbError("BatchedGasKinetics::jacobian", "negative number of states");
+    if (N == 0) return;
+    if (!T || !P || !Y || !jac) throw CtbError("BatchedGasKinetics::jacobian", "null pointer");
+    if (ldY < K) throw CtbError("BatchedGasKinetics::jacobian", "ldY is smaller than the number of species");
+    if (bufLen < N * (long long) K * K) {
+        // ArraySizeError (sourcegen/clib/templates.yaml "size_check")
+        throw CtbError("BatchedGasKinetics::jacobian", "array size (" + std::to_string(bufLen)
+                       + ") is too small; needs " + std::to_string(N * (long long) K * K));
+    }
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    JacArgs a = {};
+    a.ddCi = ddCi; a.skipThirdBodies = m_skip3b; a.skipFalloff = m_skipFalloff;
+    if (memspace == CTB_DEVICE) {
+        a.N = N; a.T = T; a.P = P; a.Y = Y; a.ldY = ldY; a.jac = jac;
+        launchJac(m_dev, a, stream());
+        cudaCheck(cudaGetLastError(), "jacKernel launch");
+        return;
+    }
+    if (memspace != CTB_HOST) throw CtbError("BatchedGasKinetics::jacobian", "memspace must be CTB_HOST or CTB_DEVICE");
+    const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) K * K);
+    long long chunk = std::max<long long>(256, std::min<long long>(N, (long long) ((256u << 20) / perState)));
+    chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 3) / 4));
+    for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
+    int b = 0;
+    for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
+        const long long n = std::min(chunk, N - n0);
+        cudaStream_t st = m_copyStream[b];
+        double* d = m_stage[b].as<double>();
+        double* dT = d; d += chunk;
+        double* dP = d; d += chunk;
+        double* dY = d; d += chunk * K;
+        double* dJ = d;
+        cudaCheck(cudaMemcpyAsync(dT, T + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D T");
+        cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
+        cudaCheck(cudaMemcpy2DAsync(dY, sizeof(double) * K, Y + n0 * ldY, sizeof(double) * ldY,
+                                    sizeof(double) * K, n, cudaMemcpyHostToDevice, st), "H2D Y");
+        a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.jac = dJ;
+        launchJac(m_dev, a, st);
+        cudaCheck(cudaGetLastError(), "jacKernel launch");
+        cudaCheck(cudaMemcpyAsync(jac + n0 * (long long) K * K, dJ, sizeof(double) * n * K * K,
+                                  cudaMemcpyDeviceToHost, st), "D2H jac");
+    }
+    cudaCheck(cudaStreamSynchronize(m_copyStream[0]), "cudaStreamSynchronize");
+    cudaCheck(cudaStreamSynchronize(m_copyStream[1]), "cudaStreamSynchronize");
+}
+
+} // namespace ctb

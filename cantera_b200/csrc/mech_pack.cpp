@@ -1,0 +1,257 @@
+// mech_pack.cpp — host-side packer: ctb_mech_tables -> contiguous device image (mech_pack.h).
+#include "mech_pack.h"
+
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+#include <stdexcept>
+
+namespace ctb {
+
+namespace {
+
+struct Blob {
+    std::vector<unsigned char> data;
+    template <class T>
+    uint32_t put(const std::vector<T>& v) {
+        while (data.size() % 16) data.push_back(0);
+        uint32_t off = (uint32_t) data.size();
+        const unsigned char* p = (const unsigned char*) v.data();
+        data.insert(data.end(), p, p + v.size() * sizeof(T));
+        return off;
+    }
+    void finish() {
+        while (data.size() % 16) data.push_back(0);
+    }
+};
+
+// The reference routes a reaction side to C1/C2/C3 when every coefficient is a whole number
+// equal to its order and the side has at most three molecules; otherwise to C_AnyN
+// (StoichManager.h:681-721).
+bool simpleSide(int n, const double* stoich, const double* order, int& molecules)
+{
+    molecules = 0;
+    for (int i = 0; i < n; i++) {
+        if (std::fmod(stoich[i], 1.0) != 0.0 || stoich[i] != order[i]) return false;
+        molecules += (int) stoich[i];
+    }
+    return n <= 3 && molecules >= 1 && molecules <= 3;
+}
+
+} // namespace
+
+PackedMech packMechanism(const ctb_mech_tables& t)
+{
+    const int K = t.n_species, R = t.n_reactions;
+    if (K < 1 || K > 65534) throw std::runtime_error("packMechanism: species count out of range");
+    if (R < 0 || R > 65534) throw std::runtime_error("packMechanism: reaction count out of range");
+    PackedMech pm;
+    MechView& v = pm.v;
+    std::memset(&v, 0, sizeof(v));
+    v.K = K;
+    v.R = R;
+    v.p_ref = t.p_ref;
+
+    // ---- execution order
+    std::vector<int> cls(R);
+    for (int i = 0; i < R; i++) {
+        switch (t.rxn_type[i]) {
+        case CTB_RATE_ARRHENIUS:
+            cls[i] = (t.rate_b[i] == 0.0 && t.rate_Ea_R[i] == 0.0) ? CLS_ARR_CONST : CLS_ARR;
+            break;
+        case CTB_RATE_LINDEMANN: cls[i] = CLS_LINDEMANN; break;
+        case CTB_RATE_TROE: cls[i] = CLS_TROE; break;
+        case CTB_RATE_SRI: cls[i] = CLS_SRI; break;
+        case CTB_RATE_TSANG: cls[i] = CLS_TSANG; break;
+        case CTB_RATE_PLOG: cls[i] = CLS_PLOG; break;
+        case CTB_RATE_CHEBYSHEV: cls[i] = CLS_CHEB; break;
+        default: throw std::runtime_error("packMechanism: unknown rate type");
+        }
+    }
+    pm.perm.resize(R);
+    std::iota(pm.perm.begin(), pm.perm.end(), 0);
+    // within a class: irreversible first (they skip the equilibrium-constant exp), then
+    // third-body flag, then reference order
+    std::stable_sort(pm.perm.begin(), pm.perm.end(), [&](int a, int b) {
+        if (cls[a] != cls[b]) return cls[a] < cls[b];
+        int ra = t.rxn_flags[a] & CTB_RXN_REVERSIBLE, rb = t.rxn_flags[b] & CTB_RXN_REVERSIBLE;
+        if (ra != rb) return ra < rb;
+        int ta = t.rxn_flags[a] & CTB_RXN_THIRD_BODY, tb = t.rxn_flags[b] & CTB_RXN_THIRD_BODY;
+        return ta < tb;
+    });
+    pm.invPerm.resize(R);
+    for (int e = 0; e < R; e++) pm.invPerm[pm.perm[e]] = e;
+    for (int c = 0; c <= CLS_COUNT; c++) v.clsBegin[c] = R;
+    for (int e = R - 1; e >= 0; e--) v.clsBegin[cls[pm.perm[e]]] = e;
+    for (int c = CLS_COUNT - 1; c >= 0; c--) v.clsBegin[c] = std::min(v.clsBegin[c], v.clsBegin[c + 1]);
+
+    // ---- species tables
+    std::vector<double> molwt(t.mol_weights, t.mol_weights + K), rmolwt(K), tmid(t.nasa_tmid, t.nasa_tmid + K);
+    for (int k = 0; k < K; k++) rmolwt[k] = 1.0 / molwt[k]; // Phase::m_rmolwts (Phase.cpp:853)
+    std::vector<double> low(t.nasa_low, t.nasa_low + 7 * K), high(t.nasa_high, t.nasa_high + 7 * K);
+
+    // ---- reaction tables
+    std::vector<double> A(R), b(R), EaR(R), mult(R), dn(R);
+    std::vector<RxnRec> rec(R);
+    std::vector<int16_t> tbIdx(R, -1), auxIdx(R, -1);
+    std::vector<double> tbDefault, tbEff, fallLow, fallCoef;
+    std::vector<int32_t> tbPtr{0}, plogPtr{0}, chebPtr{0}, chebDim, genPtr{0};
+    std::vector<uint16_t> tbSp, genSp;
+    std::vector<double> plogLogP, plogA, plogB, plogEaR, chebLim, chebCoef, genStoich, genOrder;
+    int maxChebNT = 0;
+
+    auto packSide = [&](int n, const int32_t* sp, const double* stoich, const double* order,
+                        uint16_t* slots, uint8_t& cnt) {
+        int molecules;
+        slots[0] = slots[1] = slots[2] = 0xFFFF;
+        if (n == 0) { cnt = 0; return; }
+        if (simpleSide(n, stoich, order, molecules)) {
+            int m = 0;
+            for (int i = 0; i < n; i++)
+                for (int j = 0; j < (int) stoich[i]; j++) slots[m++] = (uint16_t) sp[i];
+            cnt = (uint8_t) molecules;
+        } else {
+            cnt = SIDE_GENERAL;
+            slots[0] = (uint16_t) (genPtr.size() - 1);
+            for (int i = 0; i < n; i++) {
+                genSp.push_back((uint16_t) sp[i]);
+                genStoich.push_back(stoich[i]);
+                genOrder.push_back(order[i]);
+            }
+            genPtr.push_back((int32_t) genSp.size());
+            if (genPtr.size() - 1 > 65534) throw std::runtime_error("packMechanism: too many general sides");
+        }
+    };
+
+    for (int e = 0; e < R; e++) {
+        int i = pm.perm[e];
+        A[e] = t.rate_A[i]; b[e] = t.rate_b[i]; EaR[e] = t.rate_Ea_R[i];
+        mult[e] = t.multiplier[i]; dn[e] = t.delta_n[i];
+        RxnRec& r = rec[e];
+        r.cls = (uint8_t) cls[i];
+        r.flags = (uint8_t) t.rxn_flags[i];
+        int rb = t.reac_ptr[i], re = t.reac_ptr[i + 1], pb = t.prod_ptr[i], pe = t.prod_ptr[i + 1];
+        packSide(re - rb, t.reac_species + rb, t.reac_stoich + rb, t.reac_order + rb, r.r, r.nr);
+        packSide(pe - pb, t.prod_species + pb, t.prod_stoich + pb, t.prod_stoich + pb, r.p, r.np);
+        if (t.rxn_flags[i] & CTB_RXN_THIRD_BODY) {
+            tbIdx[e] = (int16_t) tbDefault.size();
+            tbDefault.push_back(t.tb_default[i]);
+            for (int j = t.tb_ptr[i]; j < t.tb_ptr[i + 1]; j++) {
+                tbSp.push_back((uint16_t) t.tb_species[j]);
+                tbEff.push_back(t.tb_eff[j] - t.tb_default[i]); // ThirdBodyCalc::install (:23-44)
+            }
+            tbPtr.push_back((int32_t) tbSp.size());
+        }
+        if (cls[i] >= CLS_LINDEMANN && cls[i] <= CLS_TSANG) {
+            auxIdx[e] = (int16_t) (fallLow.size() / 3);
+            fallLow.push_back(t.low_A[i]); fallLow.push_back(t.low_b[i]); fallLow.push_back(t.low_Ea_R[i]);
+            for (int j = 0; j < 5; j++) fallCoef.push_back(t.falloff_coeffs[5 * i + j]);
+        } else if (cls[i] == CLS_PLOG) {
+            auxIdx[e] = (int16_t) (plogPtr.size() - 1);
+            for (int j = t.plog_ptr[i]; j < t.plog_ptr[i + 1]; j++) {
+                plogLogP.push_back(std::log(t.plog_P[j])); // PlogRate::setRates (PlogRate.cpp:92-123)
+                plogA.push_back(t.plog_A[j]); plogB.push_back(t.plog_b[j]); plogEaR.push_back(t.plog_Ea_R[j]);
+            }
+            plogPtr.push_back((int32_t) plogLogP.size());
+        } else if (cls[i] == CLS_CHEB) {
+            auxIdx[e] = (int16_t) (chebPtr.size() - 1);
+            int nT = t.cheb_nT[i], nP = t.cheb_nP[i];
+            maxChebNT = std::max(maxChebNT, nT);
+            chebDim.push_back(nT); chebDim.push_back(nP);
+            const double* lim = t.cheb_limits + 4 * i;
+            // ChebyshevRate::setLimits (ChebyshevRate.cpp:96-112)
+            double logPmin = std::log10(lim[2]), logPmax = std::log10(lim[3]);
+            double TminInv = 1.0 / lim[0], TmaxInv = 1.0 / lim[1];
+            chebLim.push_back(-TminInv - TmaxInv);
+            chebLim.push_back(1.0 / (TmaxInv - TminInv));
+            chebLim.push_back(-logPmin - logPmax);
+            chebLim.push_back(1.0 / (logPmax - logPmin));
+            for (int j = t.cheb_ptr[i]; j < t.cheb_ptr[i + 1]; j++) chebCoef.push_back(t.cheb_coeffs[j]);
+            chebPtr.push_back((int32_t) chebCoef.size());
+        }
+    }
+    if (maxChebNT > 16) throw std::runtime_error("packMechanism: Chebyshev nT > 16 not supported");
+
+    // ---- gather lists (species-major net stoichiometry)
+    std::vector<std::vector<std::pair<int, double>>> lists(K);
+    bool fractional = false;
+    for (int e = 0; e < R; e++) {
+        int i = pm.perm[e];
+        for (int j = t.prod_ptr[i]; j < t.prod_ptr[i + 1]; j++) {
+            lists[t.prod_species[j]].push_back({e, t.prod_stoich[j]});
+        }
+        for (int j = t.reac_ptr[i]; j < t.reac_ptr[i + 1]; j++) {
+            // order-only species (stoich 0, Kinetics.cpp:750-777) stay in the list: they add
+            // nothing to the production rates but own a Jacobian column entry
+            lists[t.reac_species[j]].push_back({e, -t.reac_stoich[j]});
+        }
+    }
+    std::vector<int32_t> gPtr{0};
+    std::vector<GatherEnt> gEnt;
+    std::vector<double> gNu;
+    for (int k = 0; k < K; k++) {
+        for (auto& [e, nu] : lists[k]) {
+            GatherEnt g;
+            g.rxn = (uint16_t) e;
+            if (std::fmod(nu, 1.0) != 0.0 || std::abs(nu) > 30000) {
+                fractional = true;
+                g.nu = nu > 0 ? 1 : (nu < 0 ? -1 : 0);
+            } else {
+                g.nu = (int16_t) nu;
+            }
+            gEnt.push_back(g);
+            gNu.push_back(nu);
+        }
+        gPtr.push_back((int32_t) gEnt.size());
+    }
+
+    // ---- transposed third-body efficiencies
+    std::vector<std::vector<std::pair<int, double>>> tbT(K);
+    for (int e = 0; e < R; e++) {
+        if (tbIdx[e] < 0) continue;
+        for (int j = tbPtr[tbIdx[e]]; j < tbPtr[tbIdx[e] + 1]; j++) tbT[tbSp[j]].push_back({e, tbEff[j]});
+    }
+    std::vector<int32_t> tbTPtr{0};
+    std::vector<uint16_t> tbTRxn;
+    std::vector<double> tbTEff;
+    for (int k = 0; k < K; k++) {
+        for (auto& [e, eff] : tbT[k]) { tbTRxn.push_back((uint16_t) e); tbTEff.push_back(eff); }
+        tbTPtr.push_back((int32_t) tbTRxn.size());
+    }
+
+    // ---- lay out: hot tables first (staged to shared memory), cold tables after
+    Blob bl;
+    v.o_molwt = bl.put(molwt); v.o_rmolwt = bl.put(rmolwt); v.o_tmid = bl.put(tmid);
+    v.o_nasa_low = bl.put(low); v.o_nasa_high = bl.put(high);
+    v.o_A = bl.put(A); v.o_b = bl.put(b); v.o_EaR = bl.put(EaR); v.o_mult = bl.put(mult); v.o_dn = bl.put(dn);
+    v.o_rec = bl.put(rec);
+    v.o_tbIdx = bl.put(tbIdx); v.o_auxIdx = bl.put(auxIdx);
+    v.o_tbDefault = bl.put(tbDefault); v.o_tbPtr = bl.put(tbPtr); v.o_tbSp = bl.put(tbSp); v.o_tbEff = bl.put(tbEff);
+    v.o_tbTPtr = bl.put(tbTPtr); v.o_tbTRxn = bl.put(tbTRxn); v.o_tbTEff = bl.put(tbTEff);
+    v.o_fallLow = bl.put(fallLow); v.o_fallCoef = bl.put(fallCoef);
+    v.o_plogPtr = bl.put(plogPtr); v.o_plogLogP = bl.put(plogLogP); v.o_plogA = bl.put(plogA);
+    v.o_plogB = bl.put(plogB); v.o_plogEaR = bl.put(plogEaR);
+    v.o_chebPtr = bl.put(chebPtr); v.o_chebDim = bl.put(chebDim); v.o_chebLim = bl.put(chebLim);
+    v.o_chebCoef = bl.put(chebCoef);
+    v.o_genPtr = bl.put(genPtr); v.o_genSp = bl.put(genSp); v.o_genStoich = bl.put(genStoich);
+    v.o_genOrder = bl.put(genOrder);
+    v.o_gPtr = bl.put(gPtr); v.o_gEnt = bl.put(gEnt);
+    bl.finish();
+    v.hotBytes = (uint32_t) bl.data.size();
+    v.o_gNu = bl.put(gNu);
+    v.o_perm = bl.put(pm.perm);
+    bl.finish();
+    v.bytes = (uint32_t) bl.data.size();
+    v.nTb = (int32_t) tbDefault.size();
+    v.nFall = (int32_t) (fallLow.size() / 3);
+    v.nPlogRx = (int32_t) plogPtr.size() - 1;
+    v.nChebRx = (int32_t) chebPtr.size() - 1;
+    v.nGen = (int32_t) genPtr.size() - 1;
+    v.nGather = (int32_t) gEnt.size();
+    v.hasFractional = fractional ? 1 : 0;
+    v.maxChebNT = maxChebNT;
+    pm.blob = std::move(bl.data);
+    return pm;
+}
+
+} // namespace ctb

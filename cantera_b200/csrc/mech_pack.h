@@ -1,0 +1,123 @@
+// mech_pack.h — packed device image of a mechanism.
+//
+// The flat tables of include/ctb_clib.h (reference reaction order, CSR stoichiometry) are
+// re-laid out for the kernels: reactions are permuted into an EXECUTION ORDER grouped by rate
+// parameterisation so that the lanes of a cooperative group run the same code in one round,
+// sides with unit stoichiometry (the reference's C1/C2/C3 classes, StoichManager.h:131-326) are
+// packed into one 16-byte record, everything else goes through a general (C_AnyN) CSR side table,
+// and the net stoichiometric matrix is stored species-major ("gather lists") so that production
+// rates are a conflict-free gather instead of the reference's scatter-add
+// (StoichManager.h:732-744).
+//
+// The image is ONE contiguous 16-byte aligned blob addressed by byte offsets (MechView), so the
+// same view works on the copy in global memory and on the copy a CTA stages into shared memory
+// with a single TMA bulk copy (cp.async.bulk).
+#pragma once
+
+#include "../../include/ctb_clib.h"
+
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace ctb {
+
+// Execution classes (sort key). Reactions of one class are contiguous in execution order.
+enum RxnClass : int {
+    CLS_ARR_CONST = 0, // Arrhenius with b == 0 and Ea == 0: kf = A, no exp
+    CLS_ARR = 1,       // Arrhenius (elementary or three-body)
+    CLS_LINDEMANN = 2,
+    CLS_TROE = 3,
+    CLS_SRI = 4,
+    CLS_TSANG = 5,
+    CLS_PLOG = 6,
+    CLS_CHEB = 7,
+    CLS_COUNT = 8
+};
+
+// 16-byte per-reaction record (one 128-bit load).
+struct RxnRec {
+    uint16_t r[3];  // reactant molecule slots (species index per unit molecule), 0xFFFF unused;
+                    // if nr == SIDE_GENERAL, r[0] = index into the general-side table
+    uint16_t p[3];  // product slots, same convention
+    uint8_t nr;     // 0..3 or SIDE_GENERAL
+    uint8_t np;
+    uint8_t cls;    // RxnClass
+    uint8_t flags;  // CTB_RXN_* bits
+};
+static_assert(sizeof(RxnRec) == 16, "RxnRec must be 16 bytes");
+static const uint8_t SIDE_GENERAL = 0xFF;
+
+// Species-major gather entry: wdot_k = sum_e nu_e * q[rxn_e]. nu is signed: > 0 for a
+// product-side entry, < 0 for a reactant-side entry (the sign doubles as the role flag for
+// creation / destruction rates). Mechanisms with fractional coefficients read the signed
+// double array o_gNu instead (nu is then only the sign).
+struct GatherEnt {
+    uint16_t rxn; // execution index of the reaction
+    int16_t nu;
+};
+static_assert(sizeof(GatherEnt) == 4, "GatherEnt must be 4 bytes");
+
+// Byte offsets into the blob. Plain POD: passed to kernels by value.
+struct MechView {
+    int32_t K, R;
+    int32_t nTb;      // reactions with a third body
+    int32_t nFall;    // falloff reactions
+    int32_t nPlogRx, nChebRx, nGen; // counts of plog / chebyshev reactions and general sides
+    int32_t nGather;  // total gather entries
+    int32_t clsBegin[CLS_COUNT + 1]; // execution-order ranges per class
+    int32_t hasFractional;           // any non-integer nu in the gather lists
+    int32_t maxChebNT;
+    double p_ref;
+    // species tables
+    uint32_t o_molwt, o_rmolwt, o_tmid, o_nasa_low, o_nasa_high; // double[K], [K], [K], [K*7], [K*7]
+    // reaction tables, execution order
+    uint32_t o_A, o_b, o_EaR, o_mult, o_dn; // double[R]
+    uint32_t o_rec;                         // RxnRec[R]
+    uint32_t o_perm;                        // int32[R]: execution index -> reference index
+    uint32_t o_tbIdx;                       // int16[R]: third-body ordinal or -1
+    uint32_t o_auxIdx;                      // int16[R]: falloff / plog / cheb ordinal or -1
+    // third-body table
+    uint32_t o_tbDefault;                   // double[nTb]
+    uint32_t o_tbPtr;                       // int32[nTb+1]
+    uint32_t o_tbSp;                        // uint16[nTbEnt]
+    uint32_t o_tbEff;                       // double[nTbEnt]  (eff - default)
+    // the same efficiencies transposed (species-major), for Jacobian columns
+    uint32_t o_tbTPtr;                      // int32[K+1]
+    uint32_t o_tbTRxn;                      // uint16[nTbEnt] execution index of the reaction
+    uint32_t o_tbTEff;                      // double[nTbEnt] (eff - default)
+    // falloff table
+    uint32_t o_fallLow;                     // double[nFall*3]: A, b, Ea/R of the low-pressure limit
+    uint32_t o_fallCoef;                    // double[nFall*5]
+    // plog: per reaction group table
+    uint32_t o_plogPtr;                     // int32[nPlogRx+1] into the entry arrays
+    uint32_t o_plogLogP, o_plogA, o_plogB, o_plogEaR; // double[nPlogEnt]
+    // chebyshev
+    uint32_t o_chebPtr;                     // int32[nChebRx+1] into coefficient data
+    uint32_t o_chebDim;                     // int32[nChebRx*2]: nT, nP
+    uint32_t o_chebLim;                     // double[nChebRx*4]: TrNum, TrDen, PrNum, PrDen
+    uint32_t o_chebCoef;                    // double[...]
+    // general (C_AnyN) sides
+    uint32_t o_genPtr;                      // int32[nGen+1]
+    uint32_t o_genSp;                       // uint16[nGenEnt]
+    uint32_t o_genStoich, o_genOrder;       // double[nGenEnt]
+    // gather lists
+    uint32_t o_gPtr;                        // int32[K+1]
+    uint32_t o_gEnt;                        // GatherEnt[nGather]
+    uint32_t o_gNu;                         // double[nGather] (only read if hasFractional)
+    uint32_t bytes;                         // blob size, multiple of 16
+    uint32_t hotBytes;                      // prefix staged into shared memory (multiple of 16)
+};
+
+struct PackedMech {
+    MechView v;
+    std::vector<unsigned char> blob;
+    std::vector<int32_t> perm;    // execution -> reference
+    std::vector<int32_t> invPerm; // reference -> execution
+};
+
+//! Build the packed image. Throws std::runtime_error on unsupported input (K > 65534 ...).
+PackedMech packMechanism(const ctb_mech_tables& t);
+
+} // namespace ctb

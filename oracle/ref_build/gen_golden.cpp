@@ -159,3 +159,103 @@ static int runRhs(shared_ptr<Solution> sol, const std::string& out, size_t N, ui
     f.save(out);
     return 0;
 }
+
+// Ignition: one IdealGasConstPressureMoleReactor + ReactorNet reused across states exactly like
+// samples/cxx/openmp_ignition/openmp_ignition.cpp:60-76. Composition fuel/O2/N2 at equivalence
+// ratio phi ~ U(0.5, 2): X = {fuel: phi * 1, O2: nO2, N2: nO2 * 3.76} with nO2 = the
+// stoichiometric O2 moles per mole of fuel.
+static int runIgnite(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed,
+                     const std::string& fuel, double nO2, const std::string& o2, const std::string& n2,
+                     double Tlo, double Thi, double Plo, double Phi, double tEnd, double dTign,
+                     double rtol, double atol)
+{
+    auto gas = sol->thermo();
+    size_t K = gas->nSpecies();
+    std::mt19937_64 rng(seed);
+    std::uniform_real_distribution<double> U(0.0, 1.0);
+    auto reactor = std::make_shared<IdealGasConstPressureMoleReactor>(sol, false);
+    ReactorNet net(reactor);
+    if (rtol > 0) net.setRelativeTolerance(rtol);
+    if (atol > 0) net.setAbsoluteTolerance(atol);
+    std::vector<double> T0(N), P0(N), Y0(N * K), Tend(N), Yend(N * K), tign(N), stats(N * 8);
+    size_t kf = gas->speciesIndex(fuel), ko = gas->speciesIndex(o2), kn = gas->speciesIndex(n2);
+    for (size_t n = 0; n < N; n++) {
+        T0[n] = Tlo + (Thi - Tlo) * U(rng);
+        P0[n] = OneAtm * (Plo + (Phi - Plo) * U(rng));
+        double phi = 0.5 + 1.5 * U(rng);
+        std::vector<double> X(K, 0.0);
+        X[kf] = phi; X[ko] = nO2; X[kn] = 3.76 * nO2;
+        gas->setState_TPX(T0[n], P0[n], X);
+        gas->getMassFractions(span<double>(&Y0[n * K], K));
+        // Re-set through TPY so the engine (which takes Y) starts from the bit-identical state
+        gas->setState_TPY(T0[n], P0[n], span<const double>(&Y0[n * K], K));
+        net.setInitialTime(0.0);
+        tign[n] = std::nan("");
+        double tPrev = 0.0, TPrev = T0[n];
+        if (dTign > 0) {
+            // pass 1: the openmp_ignition.cpp:70-73 step loop, crossing time by linear
+            // interpolation between internal steps
+            while (net.time() < tEnd && std::isnan(tign[n])) {
+                double t = net.step();
+                double T = reactor->temperature();
+                if (T >= T0[n] + dTign) {
+                    tign[n] = tPrev + (t - tPrev) * (T0[n] + dTign - TPrev) / (T - TPrev);
+                }
+                tPrev = t; TPrev = T;
+            }
+            gas->setState_TPY(T0[n], P0[n], span<const double>(&Y0[n * K], K));
+            net.setInitialTime(0.0);
+        }
+        // pass 2: ReactorNet::advance (interpolated output at tEnd)
+        net.advance(tEnd);
+        Tend[n] = gas->temperature();
+        gas->getMassFractions(span<double>(&Yend[n * K], K));
+        AnyMap st = net.solverStats();
+        const char* keys[8] = {"steps", "rhs_evals", "jac_evals", "lin_solve_setups",
+                               "nonlinear_iters", "nonlinear_conv_fails", "err_test_fails",
+                               "last_order"};
+        for (int j = 0; j < 8; j++) {
+            stats[n * 8 + j] = st.hasKey(keys[j]) ? (double) st[keys[j]].asInt() : -1.0;
+        }
+    }
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) sol->kinetics()->nReactions()});
+    f.add("T", T0); f.add("P", P0); f.add("Y", Y0);
+    f.add("tEnd", std::vector<double>{tEnd}); f.add("dTign", std::vector<double>{dTign});
+    f.add("Tend", Tend); f.add("Yend", Yend); f.add("tign", tign); f.add("stats", stats);
+    f.save(out);
+    return 0;
+}
+
+int main(int argc, char** argv)
+{
+    if (argc < 7) {
+        std::cerr << "usage: gen_golden rates|ddx|rhs|ignite yaml phase out N seed [...]\n";
+        return 2;
+    }
+    try {
+        std::string mode = argv[1], phase = argv[3];
+        if (phase == "-") phase = "";
+        auto sol = newSolution(argv[2], phase, "none");
+        size_t N = std::stoul(argv[5]);
+        uint64_t seed = std::stoull(argv[6]);
+        if (mode == "rates") return runRates(sol, argv[4], N, seed);
+        if (mode == "ddx") return runDdx(sol, argv[4], N, seed);
+        if (mode == "rhs") return runRhs(sol, argv[4], N, seed);
+        if (mode == "ignite") {
+            if (argc < 17) {
+                std::cerr << "ignite needs fuel nO2 O2 N2 Tlo Thi Plo Phi tEnd dTign [rtol atol]\n";
+                return 2;
+            }
+            double rtol = argc > 17 ? std::stod(argv[17]) : -1, atol = argc > 18 ? std::stod(argv[18]) : -1;
+            return runIgnite(sol, argv[4], N, seed, argv[7], std::stod(argv[8]), argv[9], argv[10],
+                             std::stod(argv[11]), std::stod(argv[12]), std::stod(argv[13]),
+                             std::stod(argv[14]), std::stod(argv[15]), std::stod(argv[16]), rtol, atol);
+        }
+        std::cerr << "unknown mode " << mode << "\n";
+        return 2;
+    } catch (std::exception& e) {
+        std::cerr << e.what() << "\n";
+        return 1;
+    }
+}
