@@ -1,0 +1,276 @@
+"""Host-side mirror of the reference's Kinetics / ReactorNet interface for a BATCH of states.
+
+``BatchedGasKinetics`` follows ``Kinetics`` (include/cantera/kinetics/Kinetics.h:348,572,1117;
+Python names as in interfaces/cython/cantera/kinetics.pyx: ``net_production_rates``,
+``forward_rates_of_progress``, ``net_production_rates_ddX`` ...), ``BatchReactorNet`` follows
+``ReactorNet`` + ``IdealGasConstPressureMoleReactor`` (include/cantera/zeroD/ReactorNet.h:57,159).
+Every call goes through the C ABI (include/ctb_clib.h). Arrays are either numpy (host memory,
+staged by the library) or torch CUDA tensors (device memory, no copies; the call is queued on
+torch's current stream).
+"""
+import os
+
+import numpy as np
+
+from . import clib
+
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+
+
+def mechanism_path(name):
+    """Resolve 'gri30', 'gri30.yaml' or a path to the flat-table file (.ctbm) of a mechanism."""
+    if os.path.exists(name) and name.endswith(".ctbm"):
+        return name
+    base = os.path.basename(name)
+    for suffix in (".yaml", ".yml", ".ctbm"):
+        if base.endswith(suffix):
+            base = base[: -len(suffix)]
+    p = os.path.join(_DATA, base + ".ctbm")
+    if not os.path.exists(p):
+        raise clib.CtbError(
+            f"no flat mechanism table for '{name}' (looked for {p}); produce one from the YAML file with the "
+            "reference-side extractor (include/cantera_b200/MechanismExtract.h, oracle/ref_build/ctb_extract)")
+    return p
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _ptr(x):
+    return x.data_ptr() if _is_torch(x) else x.ctypes.data
+
+
+class _Batch:
+    """Validated (T, P, Y) in one memory space."""
+
+    def __init__(self, T, P, Y, K):
+        if _is_torch(T):
+            import torch
+            if not (T.is_cuda and P.is_cuda and Y.is_cuda):
+                raise clib.CtbError("torch inputs must be CUDA tensors (use numpy arrays for host memory)")
+            self.space = clib.DEVICE
+            self.T = T.contiguous().to(torch.float64)
+            self.P = P.contiguous().to(torch.float64)
+            self.Y = Y.to(torch.float64)
+            if self.Y.dim() != 2 or self.Y.stride(1) != 1:
+                self.Y = self.Y.reshape(self.T.numel(), -1).contiguous()
+            self.ldY = self.Y.stride(0) if self.Y.shape[0] > 1 else self.Y.shape[1]
+            self.N = self.T.numel()
+            self.torch = torch
+        else:
+            self.space = clib.HOST
+            self.T = np.ascontiguousarray(np.atleast_1d(T), dtype=np.float64)
+            self.P = np.ascontiguousarray(np.atleast_1d(P), dtype=np.float64)
+            self.N = self.T.size
+            self.Y = np.ascontiguousarray(Y, dtype=np.float64).reshape(self.N, -1)
+            self.ldY = self.Y.shape[1]
+            self.torch = None
+        if self.P.shape[0] != self.N or self.Y.shape[0] != self.N:
+            raise clib.CtbError("T, P and Y must describe the same number of states")
+        if self.Y.shape[1] < K:
+            raise clib.CtbError(f"Y has {self.Y.shape[1]} columns; the mechanism has {K} species")
+
+    def empty(self, *shape):
+        if self.torch is not None:
+            return self.torch.empty(shape, dtype=self.torch.float64, device=self.T.device)
+        return np.empty(shape, dtype=np.float64)
+
+
+class BatchedGasKinetics:
+    """Kinetics/BulkKinetics of one ideal-gas mechanism evaluated for N states per call."""
+
+    def __init__(self, mechanism, device=0):
+        self._lib = clib.lib()
+        self._h = clib.check(self._lib.ctb_kin_newFromFile(mechanism_path(mechanism).encode(), device))
+        self.device = device
+        self.n_species = clib.check(self._lib.ctb_kin_nSpecies(self._h))
+        self.n_reactions = clib.check(self._lib.ctb_kin_nReactions(self._h))
+
+    # ---- lifetime
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            self._lib.ctb_kin_del(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def use_torch_stream(self):
+        """Queue subsequent device-memory calls on torch's current CUDA stream."""
+        import torch
+        clib.check(self._lib.ctb_kin_setStream(self._h, torch.cuda.current_stream().cuda_stream))
+
+    def synchronize(self):
+        clib.check(self._lib.ctb_kin_synchronize(self._h))
+
+    # ---- Kinetics settings
+    def set_multiplier(self, i, f):
+        clib.check(self._lib.ctb_kin_setMultiplier(self._h, i, float(f)))
+
+    def multiplier(self, i):
+        return clib.check(self._lib.ctb_kin_multiplier(self._h, i))
+
+    def set_derivative_settings(self, skip_third_bodies=False, skip_falloff=False, rtol_delta=1e-8):
+        clib.check(self._lib.ctb_kin_setDerivativeSettings(self._h, int(skip_third_bodies), int(skip_falloff),
+                                                           float(rtol_delta)))
+
+    # ---- getters
+    def _species(self, fn, T, P, Y, out=None):
+        b = _Batch(T, P, Y, self.n_species)
+        if out is None:
+            out = b.empty(b.N, self.n_species)
+        if b.N:
+            clib.check(fn(self._h, b.N, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, _ptr(out), out.shape[1], b.space))
+        return out
+
+    def _reaction(self, fn, T, P, Y, out=None):
+        b = _Batch(T, P, Y, self.n_species)
+        if out is None:
+            out = b.empty(b.N, self.n_reactions)
+        if b.N:
+            clib.check(fn(self._h, b.N, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, _ptr(out), out.shape[1], b.space))
+        return out
+
+    def net_production_rates(self, T, P, Y, out=None):
+        """Kinetics::getNetProductionRates per state, [N, K] kmol/m^3/s."""
+        return self._species(self._lib.ctb_kin_getNetProductionRates, T, P, Y, out)
+
+    def creation_rates(self, T, P, Y, out=None):
+        return self._species(self._lib.ctb_kin_getCreationRates, T, P, Y, out)
+
+    def destruction_rates(self, T, P, Y, out=None):
+        return self._species(self._lib.ctb_kin_getDestructionRates, T, P, Y, out)
+
+    def forward_rates_of_progress(self, T, P, Y, out=None):
+        return self._reaction(self._lib.ctb_kin_getFwdRatesOfProgress, T, P, Y, out)
+
+    def reverse_rates_of_progress(self, T, P, Y, out=None):
+        return self._reaction(self._lib.ctb_kin_getRevRatesOfProgress, T, P, Y, out)
+
+    def net_rates_of_progress(self, T, P, Y, out=None):
+        return self._reaction(self._lib.ctb_kin_getNetRatesOfProgress, T, P, Y, out)
+
+    def forward_rate_constants(self, T, P, Y, out=None):
+        return self._reaction(self._lib.ctb_kin_getFwdRateConstants, T, P, Y, out)
+
+    def equilibrium_constants(self, T, P, Y, out=None):
+        return self._reaction(self._lib.ctb_kin_getEquilibriumConstants, T, P, Y, out)
+
+    def _jac(self, fn, T, P, Y, out):
+        b = _Batch(T, P, Y, self.n_species)
+        K = self.n_species
+        if out is None:
+            out = b.empty(b.N, K, K)
+        if b.N:
+            buf_len = out.numel() if _is_torch(out) else out.size
+            clib.check(fn(self._h, b.N, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, _ptr(out), buf_len, b.space))
+        return out
+
+    def net_production_rates_ddX(self, T, P, Y, out=None):
+        """Kinetics::netProductionRates_ddX per state as [N, K, K] with out[n, j, k] = d wdot_k / d X_j
+        (the column-major K x K buffer of kin_getNetProductionRates_ddX)."""
+        return self._jac(self._lib.ctb_kin_getNetProductionRates_ddX, T, P, Y, out)
+
+    def net_production_rates_ddCi(self, T, P, Y, out=None):
+        return self._jac(self._lib.ctb_kin_getNetProductionRates_ddCi, T, P, Y, out)
+
+
+class BatchReactorNet:
+    """N x (IdealGasConstPressureMoleReactor + ReactorNet) advanced together."""
+
+    def __init__(self, kinetics, n_reactors):
+        self._lib = clib.lib()
+        self.kinetics = kinetics
+        self.n_reactors = int(n_reactors)
+        self._h = clib.check(self._lib.ctb_reactornet_new(kinetics.handle, self.n_reactors))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            self._lib.ctb_reactornet_del(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_state(self, T, P, Y):
+        b = _Batch(T, P, Y, self.kinetics.n_species)
+        if b.N != self.n_reactors:
+            raise clib.CtbError(f"expected {self.n_reactors} states, got {b.N}")
+        clib.check(self._lib.ctb_reactornet_setState(self._h, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, b.space))
+
+    @property
+    def rtol(self):
+        return self._rtol
+
+    @rtol.setter
+    def rtol(self, v):
+        clib.check(self._lib.ctb_reactornet_setRelativeTolerance(self._h, float(v)))
+        self._rtol = float(v)
+
+    @property
+    def atol(self):
+        return self._atol
+
+    @atol.setter
+    def atol(self, v):
+        clib.check(self._lib.ctb_reactornet_setAbsoluteTolerance(self._h, float(v)))
+        self._atol = float(v)
+
+    def set_max_steps(self, n):
+        clib.check(self._lib.ctb_reactornet_setMaxSteps(self._h, int(n)))
+
+    def set_initial_time(self, t0):
+        clib.check(self._lib.ctb_reactornet_setInitialTime(self._h, float(t0)))
+
+    def set_ignition_monitor(self, dT):
+        clib.check(self._lib.ctb_reactornet_setIgnitionMonitor(self._h, float(dT)))
+
+    def advance(self, t):
+        clib.check(self._lib.ctb_reactornet_advance(self._h, float(t)))
+
+    @property
+    def time(self):
+        return clib.check(self._lib.ctb_reactornet_time(self._h))
+
+    def get_state(self, device_like=None):
+        """(T[N], Y[N, K]) of the reactor contents; torch CUDA tensors if ``device_like`` is one."""
+        K = self.kinetics.n_species
+        if device_like is not None and _is_torch(device_like):
+            import torch
+            T = torch.empty(self.n_reactors, dtype=torch.float64, device=device_like.device)
+            Y = torch.empty(self.n_reactors, K, dtype=torch.float64, device=device_like.device)
+            space = clib.DEVICE
+        else:
+            T = np.empty(self.n_reactors)
+            Y = np.empty((self.n_reactors, K))
+            space = clib.HOST
+        clib.check(self._lib.ctb_reactornet_getState(self._h, _ptr(T), _ptr(Y), K, space))
+        return T, Y
+
+    def status(self):
+        s = np.empty(self.n_reactors, dtype=np.int32)
+        clib.check(self._lib.ctb_reactornet_status(self._h, s.size, s.ctypes.data))
+        return s
+
+    def solver_stats(self):
+        """[N, 8] counters: steps, rhs_evals, jac_evals, lin_solve_setups, nonlinear_iters,
+        nonlinear_conv_fails, err_test_fails, last_order (ReactorNet::solverStats)."""
+        s = np.empty((self.n_reactors, clib.NSTATS), dtype=np.int64)
+        clib.check(self._lib.ctb_reactornet_solverStats(self._h, s.size, s.ctypes.data))
+        return s
+
+    def ignition_delay(self):
+        t = np.empty(self.n_reactors)
+        clib.check(self._lib.ctb_reactornet_ignitionDelay(self._h, t.size, t.ctypes.data))
+        return t

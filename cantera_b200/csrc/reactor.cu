@@ -1,0 +1,186 @@
+// reactor.cu — BatchReactorNet host side: device-resident reactor states, staging, launches.
+#include "reactor.h"
+
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace ctb {
+
+BatchReactorNet::BatchReactorNet(std::shared_ptr<BatchedGasKinetics> kin, long long nReactors)
+    : m_kin(std::move(kin)), m_N(nReactors)
+{
+    if (!m_kin) throw CtbError("BatchReactorNet", "null kinetics object");
+    if (nReactors < 1) throw CtbError("BatchReactorNet", "the number of reactors must be positive");
+    m_neq = m_kin->nSpecies() + 1;
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    const size_t N = (size_t) m_N;
+    m_y.reserve(sizeof(double) * N * m_neq);
+    m_P.reserve(sizeof(double) * N);
+    m_T0.reserve(sizeof(double) * N);
+    m_hist.reserve(sizeof(double) * N * (size_t) reactorHistDoubles(m_neq));
+    m_tIgn.reserve(sizeof(double) * N);
+    m_status.reserve(sizeof(int32_t) * N);
+    m_stats.reserve(sizeof(long long) * N * CTB_NSTATS);
+    m_counter.reserve(sizeof(unsigned long long));
+    cudaCheck(cudaMemsetAsync(m_status.p, 0, sizeof(int32_t) * N, m_kin->stream()), "cudaMemset");
+    cudaCheck(cudaMemsetAsync(m_stats.p, 0, sizeof(long long) * N * CTB_NSTATS, m_kin->stream()), "cudaMemset");
+    cudaCheck(cudaMemsetAsync(m_tIgn.p, 0xFF, sizeof(double) * N, m_kin->stream()), "cudaMemset"); // NaN
+}
+
+BatchReactorNet::~BatchReactorNet()
+{
+    cudaSetDevice(m_kin->device());
+    cudaStreamSynchronize(m_kin->stream());
+}
+
+void BatchReactorNet::setState(const double* T, const double* P, const double* Y, long long ldY, int memspace)
+{
+    const int K = m_neq - 1;
+    if (!T || !P || !Y) throw CtbError("BatchReactorNet::setState", "null state pointer");
+    if (ldY < K) throw CtbError("BatchReactorNet::setState", "ldY is smaller than the number of species");
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    const double *dT = T, *dP = P, *dY = Y;
+    long long ld = ldY;
+    if (memspace == CTB_HOST) {
+        m_io.reserve(sizeof(double) * (size_t) m_N * (K + 2));
+        double* d = m_io.as<double>();
+        cudaCheck(cudaMemcpyAsync(d, T, sizeof(double) * m_N, cudaMemcpyHostToDevice, st), "H2D T");
+        cudaCheck(cudaMemcpyAsync(d + m_N, P, sizeof(double) * m_N, cudaMemcpyHostToDevice, st), "H2D P");
+        cudaCheck(cudaMemcpy2DAsync(d + 2 * m_N, sizeof(double) * K, Y, sizeof(double) * ldY, sizeof(double) * K,
+                                    m_N, cudaMemcpyHostToDevice, st), "H2D Y");
+        dT = d; dP = d + m_N; dY = d + 2 * m_N; ld = K;
+    } else if (memspace != CTB_DEVICE) {
+        throw CtbError("BatchReactorNet::setState", "memspace must be CTB_HOST or CTB_DEVICE");
+    }
+    launchReactorInit(m_kin->mech(), m_N, dT, dP, dY, ld, m_y.as<double>(), m_P.as<double>(),
+                      m_T0.as<double>(), st);
+    cudaCheck(cudaGetLastError(), "reactorInit launch");
+    cudaCheck(cudaMemsetAsync(m_status.p, 0, sizeof(int32_t) * m_N, st), "cudaMemset");
+    cudaCheck(cudaMemsetAsync(m_stats.p, 0, sizeof(long long) * m_N * CTB_NSTATS, st), "cudaMemset");
+    cudaCheck(cudaMemsetAsync(m_tIgn.p, 0xFF, sizeof(double) * m_N, st), "cudaMemset");
+    if (memspace == CTB_HOST) cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    m_haveState = true;
+    m_time = 0.0;   // ReactorNet::setInitialTime(0)
+    m_restart = true;
+}
+
+void BatchReactorNet::setRelativeTolerance(double rtol)
+{
+    if (!(rtol > 0.0)) {
+        throw CtbError("BatchReactorNet::setRelativeTolerance",
+                       "Relative tolerance must be positive; got " + std::to_string(rtol) + ".");
+    }
+    m_rtol = rtol;
+    m_restart = true; // CVodesIntegrator::setTolerances takes effect at the next (re)initialisation
+}
+
+void BatchReactorNet::setAbsoluteTolerance(double atol)
+{
+    if (!(atol > 0.0)) {
+        throw CtbError("BatchReactorNet::setAbsoluteTolerance",
+                       "Absolute tolerance must be positive; got " + std::to_string(atol) + ".");
+    }
+    m_atol = atol;
+    m_atolUser = true;
+    m_restart = true;
+}
+
+void BatchReactorNet::setMaxSteps(int n)
+{
+    if (n < 1) throw CtbError("BatchReactorNet::setMaxSteps", "the number of steps must be positive");
+    m_maxSteps = n;
+}
+
+void BatchReactorNet::setInitialTime(double t0)
+{
+    m_time = t0;
+    m_restart = true;
+}
+
+void BatchReactorNet::setIgnitionMonitor(double dT)
+{
+    m_ignDT = dT;
+}
+
+void BatchReactorNet::advance(double t)
+{
+    if (!m_haveState) throw CtbError("BatchReactorNet::advance", "setState has not been called");
+    if (t == m_time) return; // CVodesIntegrator::integrate (CVodesIntegrator.cpp:481-483)
+    if (t < m_time) {
+        throw CtbError("BatchReactorNet::advance", "Cannot integrate backwards in time.\nRequested time "
+                       + std::to_string(t) + " < current time " + std::to_string(m_time));
+    }
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    cudaCheck(cudaMemsetAsync(m_counter.p, 0, sizeof(unsigned long long), st), "cudaMemset");
+    ReactorBatch b = {};
+    b.N = m_N; b.neq = m_neq;
+    b.y = m_y.as<double>(); b.P = m_P.as<double>(); b.T0 = m_T0.as<double>();
+    b.hist = m_hist.as<double>(); b.histStride = reactorHistDoubles(m_neq);
+    b.tIgn = m_tIgn.as<double>(); b.status = m_status.as<int32_t>(); b.stats = m_stats.as<long long>();
+    b.counter = m_counter.as<unsigned long long>();
+    b.t0 = m_time; b.tout = t; b.rtol = m_rtol; b.atol = m_atol; b.atolUser = m_atolUser;
+    b.maxSteps = m_maxSteps; b.restart = m_restart; b.ignDT = m_ignDT;
+    launchAdvance(m_kin->mech(), b, st);
+    cudaCheck(cudaGetLastError(), "advance launch");
+    m_time = t;
+    m_restart = false;
+}
+
+void BatchReactorNet::getState(double* T, double* Y, long long ldY, int memspace)
+{
+    const int K = m_neq - 1;
+    if (!m_haveState) throw CtbError("BatchReactorNet::getState", "setState has not been called");
+    if (!T || !Y) throw CtbError("BatchReactorNet::getState", "null output pointer");
+    if (ldY < K) throw CtbError("BatchReactorNet::getState", "ldY is smaller than the number of species");
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    if (memspace == CTB_DEVICE) {
+        launchReactorContents(m_kin->mech(), m_N, m_y.as<double>(), T, Y, ldY, st);
+        cudaCheck(cudaGetLastError(), "reactorContents launch");
+        return;
+    }
+    if (memspace != CTB_HOST) throw CtbError("BatchReactorNet::getState", "memspace must be CTB_HOST or CTB_DEVICE");
+    m_io.reserve(sizeof(double) * (size_t) m_N * (K + 2));
+    double* d = m_io.as<double>();
+    launchReactorContents(m_kin->mech(), m_N, m_y.as<double>(), d, d + m_N, K, st);
+    cudaCheck(cudaGetLastError(), "reactorContents launch");
+    cudaCheck(cudaMemcpyAsync(T, d, sizeof(double) * m_N, cudaMemcpyDeviceToHost, st), "D2H T");
+    cudaCheck(cudaMemcpy2DAsync(Y, sizeof(double) * ldY, d + m_N, sizeof(double) * K, sizeof(double) * K, m_N,
+                                cudaMemcpyDeviceToHost, st), "D2H Y");
+    cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+}
+
+void BatchReactorNet::status(long long len, int32_t* out)
+{
+    if (len < m_N || !out) throw CtbError("BatchReactorNet::status", "array size (" + std::to_string(len)
+                                          + ") is too small; needs " + std::to_string(m_N));
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaCheck(cudaMemcpyAsync(out, m_status.p, sizeof(int32_t) * m_N, cudaMemcpyDeviceToHost, m_kin->stream()), "D2H");
+    cudaCheck(cudaStreamSynchronize(m_kin->stream()), "cudaStreamSynchronize");
+}
+
+void BatchReactorNet::solverStats(long long len, long long* out)
+{
+    if (len < m_N * CTB_NSTATS || !out) {
+        throw CtbError("BatchReactorNet::solverStats", "array size (" + std::to_string(len)
+                       + ") is too small; needs " + std::to_string(m_N * CTB_NSTATS));
+    }
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaCheck(cudaMemcpyAsync(out, m_stats.p, sizeof(long long) * m_N * CTB_NSTATS, cudaMemcpyDeviceToHost,
+                              m_kin->stream()), "D2H");
+    cudaCheck(cudaStreamSynchronize(m_kin->stream()), "cudaStreamSynchronize");
+}
+
+void BatchReactorNet::ignitionDelay(long long len, double* out)
+{
+    if (len < m_N || !out) throw CtbError("BatchReactorNet::ignitionDelay", "array size (" + std::to_string(len)
+                                          + ") is too small; needs " + std::to_string(m_N));
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaCheck(cudaMemcpyAsync(out, m_tIgn.p, sizeof(double) * m_N, cudaMemcpyDeviceToHost, m_kin->stream()), "D2H");
+    cudaCheck(cudaStreamSynchronize(m_kin->stream()), "cudaStreamSynchronize");
+}
+
+} // namespace ctb
