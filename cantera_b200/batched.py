@@ -63,7 +63,8 @@ class _Batch:
             self.T = np.ascontiguousarray(np.atleast_1d(T), dtype=np.float64)
             self.P = np.ascontiguousarray(np.atleast_1d(P), dtype=np.float64)
             self.N = self.T.size
-            self.Y = np.ascontiguousarray(Y, dtype=np.float64).reshape(self.N, -1)
+            Y = np.ascontiguousarray(Y, dtype=np.float64)
+            self.Y = Y.reshape(self.N, -1) if self.N else Y.reshape(0, K)
             self.ldY = self.Y.shape[1]
             self.torch = None
         if self.P.shape[0] != self.N or self.Y.shape[0] != self.N:
@@ -257,6 +258,18 @@ class BatchReactorNet:
             space = clib.HOST
         clib.check(self._lib.ctb_reactornet_getState(self._h, _ptr(T), _ptr(Y), K, space))
         return T, Y
+
+    def get_state_vector(self):
+        """ReactorNet::getState: [N, K+1] rows [T, n_1..n_K] (host)."""
+        y = np.empty((self.n_reactors, self.kinetics.n_species + 1))
+        clib.check(self._lib.ctb_reactornet_getStateVector(self._h, y.ctypes.data, y.size, clib.HOST))
+        return y
+
+    def eval(self):
+        """ReactorNet::eval at the current state: ydot [N, K+1] (host)."""
+        yd = np.empty((self.n_reactors, self.kinetics.n_species + 1))
+        clib.check(self._lib.ctb_reactornet_eval(self._h, yd.ctypes.data, yd.size, clib.HOST))
+        return yd
 
     def status(self):
         s = np.empty(self.n_reactors, dtype=np.int32)

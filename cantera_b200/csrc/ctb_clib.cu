@@ -284,6 +284,16 @@ int32_t ctb_reactornet_getState(int32_t handle, double* T, double* Y, int64_t ld
     return guard([&] { NetCabinet::at(handle)->getState(T, Y, ldY, memspace); return 0; });
 }
 
+int32_t ctb_reactornet_getStateVector(int32_t handle, double* y, int64_t bufLen, int32_t memspace)
+{
+    return guard([&] { NetCabinet::at(handle)->getStateVector(y, bufLen, memspace); return 0; });
+}
+
+int32_t ctb_reactornet_eval(int32_t handle, double* ydot, int64_t bufLen, int32_t memspace)
+{
+    return guard([&] { NetCabinet::at(handle)->eval(ydot, bufLen, memspace); return 0; });
+}
+
 int32_t ctb_reactornet_status(int32_t handle, int64_t len, int32_t* status)
 {
     return guard([&] { NetCabinet::at(handle)->status(len, status); return 0; });

@@ -59,7 +59,7 @@ public:
     //! Kinetics::setDerivativeSettings (BulkKinetics.cpp:259-282)
     void setDerivativeSettings(bool skipThirdBodies, bool skipFalloff, double rtolDelta);
 
-    void setStream(cudaStream_t s) { m_userStream = s; m_hasUserStream = s != nullptr; }
+    void setStream(cudaStream_t s) { m_userStream = s; m_hasUserStream = true; }
     cudaStream_t stream() const { return m_hasUserStream ? m_userStream : m_stream; }
     void synchronize();
 

@@ -153,6 +153,40 @@ void BatchReactorNet::getState(double* T, double* Y, long long ldY, int memspace
     cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
 }
 
+void BatchReactorNet::getStateVector(double* y, long long bufLen, int memspace)
+{
+    if (!m_haveState) throw CtbError("BatchReactorNet::getStateVector", "setState has not been called");
+    const long long need = m_N * m_neq;
+    if (!y || bufLen < need) throw CtbError("BatchReactorNet::getStateVector", "array size (" + std::to_string(bufLen)
+                                            + ") is too small; needs " + std::to_string(need));
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    cudaCheck(cudaMemcpyAsync(y, m_y.p, sizeof(double) * need,
+                              memspace == CTB_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st), "copy y");
+    if (memspace != CTB_DEVICE) cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+}
+
+void BatchReactorNet::eval(double* ydot, long long bufLen, int memspace)
+{
+    if (!m_haveState) throw CtbError("BatchReactorNet::eval", "setState has not been called");
+    const long long need = m_N * m_neq;
+    if (!ydot || bufLen < need) throw CtbError("BatchReactorNet::eval", "array size (" + std::to_string(bufLen)
+                                               + ") is too small; needs " + std::to_string(need));
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    double* d = ydot;
+    if (memspace != CTB_DEVICE) {
+        m_io.reserve(sizeof(double) * (size_t) need);
+        d = m_io.as<double>();
+    }
+    launchReactorEval(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st);
+    cudaCheck(cudaGetLastError(), "eval launch");
+    if (memspace != CTB_DEVICE) {
+        cudaCheck(cudaMemcpyAsync(ydot, d, sizeof(double) * need, cudaMemcpyDeviceToHost, st), "D2H ydot");
+        cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    }
+}
+
 void BatchReactorNet::status(long long len, int32_t* out)
 {
     if (len < m_N || !out) throw CtbError("BatchReactorNet::status", "array size (" + std::to_string(len)

@@ -46,6 +46,9 @@ void launchReactorInit(const DeviceMech& m, long long N, const double* T, const 
 //! (T, Y) of the contents (Phase::setMolesNoTruncate -> massFractions)
 void launchReactorContents(const DeviceMech& m, long long N, const double* y, double* T, double* Y,
                            long long ldY, cudaStream_t stream);
+//! ydot = ReactorNet::eval at the current solution vectors
+void launchReactorEval(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+                       cudaStream_t stream);
 //! doubles of integrator memory per reactor
 long long reactorHistDoubles(int neq);
 
@@ -66,6 +69,10 @@ public:
     void advance(double t);                 // ReactorNet.cpp:351-357
     double time() const { return m_time; }
     void getState(double* T, double* Y, long long ldY, int memspace);
+    //! ReactorNet::getState (ReactorNet.cpp:688-695): y[n*(K+1) + i] = [T, n_1..n_K] of every reactor
+    void getStateVector(double* y, long long bufLen, int memspace);
+    //! ReactorNet::eval (ReactorNet.cpp:617-635) at the current state: ydot[n*(K+1) + i]
+    void eval(double* ydot, long long bufLen, int memspace);
     void status(long long len, int32_t* out);
     void solverStats(long long len, long long* out);
     void setIgnitionMonitor(double dT);

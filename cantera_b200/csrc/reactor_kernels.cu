@@ -1,8 +1,275 @@
-// TEMPORARY stub (replaced by the BDF kernels)
-#include "reactor.h"
+// reactor_kernels.cu — kernels of BatchReactorNet.
+//
+//   advanceKernel<NT>   persistent CTAs; each cooperative group of NT threads pulls reactors from a
+//                       global work queue (reactors differ ~10x in step count) and integrates one
+//                       at a time with the BDF/Newton solver of bdf.cuh, entirely out of shared
+//                       memory: per reactor, HBM sees y in, y + integrator memory out.
+//   reactorInitKernel   getState of a fresh reactor from (T, P, Y)
+//   reactorContentsKernel (T, Y) of the contents from the solution vector
+#include "bdf.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <stdexcept>
+
 namespace ctb {
-long long reactorHistDoubles(int neq) { return 8LL * neq + 32; }
-void launchAdvance(const DeviceMech&, const ReactorBatch&, cudaStream_t) { throw CtbError("advance", "not implemented"); }
-void launchReactorInit(const DeviceMech&, long long, const double*, const double*, const double*, long long, double*, double*, double*, cudaStream_t) { throw CtbError("reactorInit", "not implemented"); }
-void launchReactorContents(const DeviceMech&, long long, const double*, double*, double*, long long, cudaStream_t) { throw CtbError("reactorContents", "not implemented"); }
+
+long long reactorHistDoubles(int neq) { return 6LL * neq + BDF_HIST_SCALARS; }
+
+namespace {
+
+template <int NT>
+__global__ void __launch_bounds__(512) advanceKernel(const MechView v, const unsigned char* __restrict__ gmech,
+                                                     const ReactorBatch a, const int groupDoubles)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + v.hotBytes);
+    tmaStage(smem, gmech, v.hotBytes, bar);
+    const unsigned char* sm = smem;
+
+    using G = NamedGroup<NT>;
+    const int gInCta = threadIdx.x / NT;
+    double* base = reinterpret_cast<double*>(smem + v.hotBytes + 16) + (size_t) gInCta * groupDoubles;
+    const G g(base, 1 + gInCta);
+    const ReactorWork wk = carveWork(base + 16, v.K, v.R);
+    const int n = wk.n;
+    Bdf<G> bdf(g, v, sm, gmech, wk);
+    bdf.rtol = a.rtol;
+    bdf.atolT = a.atol;
+
+    for (;;) {
+        // ---- next reactor from the queue
+        long long r;
+        if (NT == 32) {
+            unsigned long long t = 0;
+            if (g.lane() == 0) t = atomicAdd(a.counter, 1ULL);
+            r = (long long) __shfl_sync(0xffffffffu, t, 0);
+        } else {
+            g.sync();
+            if (g.lane() == 0) base[8] = (double) atomicAdd(a.counter, 1ULL);
+            g.sync();
+            r = (long long) base[8];
+        }
+        if (r >= a.N) break;
+        if (a.status[r] != CTB_STATUS_OK && !a.restart) continue; // failed earlier: stays failed
+
+        double* yg = a.y + r * n;
+        double* hist = a.hist + r * a.histStride;
+        bdf.P = a.P[r];
+        bdf.nfe = bdf.nsetups = bdf.nni = bdf.ncfn = bdf.netf = 0;
+        int status = CTB_STATUS_OK;
+        if (a.restart) {
+            double moles = 0.0;
+            for (int i = g.lane(); i < n; i += NT) {
+                const double yi = yg[i];
+                wk.zn[i] = yi;
+                if (i > 0) moles += yi;
+            }
+            moles = g.sum(moles);
+            // MoleReactor::updateDefaultTolerances (MoleReactor.cpp:64-76): atol * total moles for
+            // the species rows unless the user set an absolute tolerance (ReactorNet.cpp:233-245)
+            bdf.atolS = (a.atolUser || !(moles > 0.0)) ? a.atol : a.atol * moles;
+            g.sync();
+            status = bdf.start(a.t0, a.tout);
+        } else {
+            bdf.load(hist);
+            g.sync();
+        }
+        const int nst0 = bdf.nst;
+        const double Tign = a.ignDT > 0.0 ? a.T0[r] + a.ignDT : 0.0;
+        bool ignPending = a.ignDT > 0.0 && !(a.tIgn[r] == a.tIgn[r]);
+        double tPrev = bdf.tn, TPrev = wk.zn[0];
+        while (status == CTB_STATUS_OK && bdf.tn < a.tout) {
+            if (bdf.nst - nst0 >= a.maxSteps) {
+                status = CTB_STATUS_TOO_MANY_STEPS;
+                break;
+            }
+            if (bdf.nst > 0) bdf.setEwt(wk.zn);
+            status = bdf.step();
+            if (status != CTB_STATUS_OK) break;
+            const double Tnow = wk.zn[0];
+            if (!(Tnow == Tnow)) {
+                status = CTB_STATUS_NOT_FINITE;
+                break;
+            }
+            if (ignPending && Tnow >= Tign) {
+                // first crossing of T0 + dT, linear in the step (openmp_ignition.cpp:70-73)
+                if (g.lane() == 0) a.tIgn[r] = tPrev + (bdf.tn - tPrev) * (Tign - TPrev) / (Tnow - TPrev);
+                ignPending = false;
+            }
+            tPrev = bdf.tn;
+            TPrev = Tnow;
+        }
+        g.sync();
+        if (status == CTB_STATUS_OK) {
+            bdf.interpolate(a.tout, yg);
+        } else {
+            for (int i = g.lane(); i < n; i += NT) yg[i] = wk.zn[i];
+        }
+        bdf.save(hist);
+        if (g.lane() == 0) {
+            a.status[r] = status;
+            long long* st = a.stats + r * CTB_NSTATS;
+            st[STAT_STEPS] += bdf.nst - nst0;
+            st[STAT_RHS] += bdf.nfe;
+            st[STAT_JAC] += bdf.nsetups;
+            st[STAT_SETUPS] += bdf.nsetups;
+            st[STAT_NLITERS] += bdf.nni;
+            st[STAT_NCFAILS] += bdf.ncfn;
+            st[STAT_ETFAILS] += bdf.netf;
+            st[STAT_ORDER] = bdf.q;
+        }
+    }
 }
+
+// ReactorNet::eval (ReactorNet.cpp:617-635) for every reactor at its current solution vector:
+// a warp per reactor.
+__global__ void __launch_bounds__(256) evalKernel(const MechView v, const unsigned char* __restrict__ gmech,
+                                                  long long N, const double* __restrict__ y,
+                                                  const double* __restrict__ P, double* __restrict__ ydot,
+                                                  const int groupDoubles)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + v.hotBytes);
+    tmaStage(smem, gmech, v.hotBytes, bar);
+    using G = NamedGroup<32>;
+    const int gInCta = threadIdx.x / 32;
+    double* base = reinterpret_cast<double*>(smem + v.hotBytes + 16) + (size_t) gInCta * groupDoubles;
+    const G g(base, 1 + gInCta);
+    const int K = v.K, n = K + 1;
+    ReactorWork wk = {};
+    wk.n = n;
+    wk.y = base; wk.f = wk.y + n; wk.c = wk.f + n; wk.grt = wk.c + K; wk.hrt = wk.grt + K; wk.cpr = wk.hrt + K;
+    wk.q = wk.cpr + K;
+    const long long stride = (long long) gridDim.x * (blockDim.x / 32);
+    for (long long r = (long long) blockIdx.x * (blockDim.x / 32) + gInCta; r < N; r += stride) {
+        for (int i = g.lane(); i < n; i += 32) wk.y[i] = y[r * n + i];
+        g.sync();
+        RhsAux aux;
+        reactorRhs<G, false>(g, v, smem, gmech, wk, P[r], wk.y, wk.f, aux);
+        for (int i = g.lane(); i < n; i += 32) ydot[r * n + i] = wk.f[i];
+        g.sync();
+    }
+}
+
+// One thread per reactor: Phase::setMassFractions (Phase.cpp:342-360) + setState_TP, then
+// IdealGasConstPressureMoleReactor::getState (:22-30) with m_vol = 1 m^3: y = [T, m Y_k / W_k].
+__global__ void reactorInitKernel(const MechView v, const unsigned char* __restrict__ gmech, long long N,
+                                  const double* __restrict__ T, const double* __restrict__ P,
+                                  const double* __restrict__ Y, long long ldY, double* __restrict__ y,
+                                  double* __restrict__ Pout, double* __restrict__ T0)
+{
+    const long long r = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= N) return;
+    const int K = v.K;
+    const double* rmolwt = CTB_TAB(double, gmech, v.o_rmolwt);
+    const double* Yr = Y + r * ldY;
+    double sum = 0.0;
+    for (int k = 0; k < K; k++) sum += fmax(Yr[k], 0.0);
+    const double invSum = 1.0 / sum;
+    double sym = 0.0;
+    for (int k = 0; k < K; k++) sym += (fmax(Yr[k], 0.0) * invSum) * rmolwt[k];
+    const double mmw = 1.0 / sym;
+    const double dens = P[r] * mmw / (T[r] * CTB_GAS_CONSTANT);
+    const double mass = dens * 1.0;
+    double* yr = y + r * (K + 1);
+    yr[0] = T[r];
+    for (int k = 0; k < K; k++) yr[1 + k] = mass * rmolwt[k] * (fmax(Yr[k], 0.0) * invSum);
+    Pout[r] = P[r];
+    T0[r] = T[r];
+}
+
+__global__ void reactorContentsKernel(const MechView v, const unsigned char* __restrict__ gmech, long long N,
+                                      const double* __restrict__ y, double* __restrict__ T,
+                                      double* __restrict__ Y, long long ldY)
+{
+    const long long r = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= N) return;
+    const int K = v.K;
+    const double* molwt = CTB_TAB(double, gmech, v.o_molwt);
+    const double* yr = y + r * (K + 1);
+    double totalMass = 0.0;
+    for (int k = 0; k < K; k++) totalMass += yr[1 + k] * molwt[k];
+    const double f = 1.0 / totalMass;
+    for (int k = 0; k < K; k++) Y[r * ldY + k] = (yr[1 + k] * molwt[k]) * f;
+    T[r] = yr[0];
+}
+
+template <int NT>
+bool launchAdvanceT(const DeviceMech& m, const ReactorBatch& b, int maxThreads, cudaStream_t stream)
+{
+    const MechView& v = m.view;
+    const size_t groupDoubles = 16 + reactorWorkDoubles(v.K, v.R);
+    const size_t fixed = v.hotBytes + 16;
+    const size_t budget = (size_t) m.smemOptIn - 1024;
+    if (fixed + groupDoubles * 8 > budget) return false;
+    int groups = (int) ((budget - fixed) / (groupDoubles * 8));
+    groups = std::min(groups, std::min(15, maxThreads / NT));
+    if (groups < 1) return false;
+    const size_t smemBytes = fixed + (size_t) groups * groupDoubles * 8;
+    auto kern = advanceKernel<NT>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
+    const long long want = (b.N + groups - 1) / groups;
+    const int grid = (int) std::max<long long>(1, std::min<long long>(want, m.numSMs));
+    kern<<<grid, groups * NT, smemBytes, stream>>>(v, m.dBlob, b, (int) groupDoubles);
+    return true;
+}
+
+} // namespace
+
+void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stream)
+{
+    if (b.N <= 0) return;
+    const MechView& v = m.view;
+    // lanes per reactor: the number of reactors resident on an SM is bounded by shared memory
+    // (one Newton matrix each), so the group is widened until ~512 threads are busy
+    const size_t groupBytes = (16 + reactorWorkDoubles(v.K, v.R)) * 8;
+    const size_t budget = (size_t) m.smemOptIn - 1024 - v.hotBytes - 16;
+    const int fit = (int) std::max<size_t>(1, budget / groupBytes);
+    int nt = 32;
+    while (nt < 256 && fit * nt * 2 <= 512) nt *= 2;
+    if (const char* e = std::getenv("CTB_BDF_NT")) nt = std::atoi(e);
+    bool ok;
+    switch (nt) {
+    case 32: ok = launchAdvanceT<32>(m, b, 512, stream); break;
+    case 64: ok = launchAdvanceT<64>(m, b, 512, stream); break;
+    case 128: ok = launchAdvanceT<128>(m, b, 512, stream); break;
+    case 256: ok = launchAdvanceT<256>(m, b, 512, stream); break;
+    default: throw std::runtime_error("CTB_BDF_NT must be 32, 64, 128 or 256");
+    }
+    if (!ok) throw std::runtime_error("mechanism too large for the shared-memory reactor kernel");
+}
+
+void launchReactorEval(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+                       cudaStream_t stream)
+{
+    if (N <= 0) return;
+    const MechView& v = m.view;
+    const int groupDoubles = (2 * (v.K + 1) + 4 * v.K + v.R + 1) & ~1;
+    const int groups = 8;
+    const size_t smemBytes = v.hotBytes + 16 + (size_t) groups * groupDoubles * 8;
+    if (smemBytes > (size_t) m.smemOptIn - 1024) throw std::runtime_error("mechanism too large for the eval kernel");
+    cudaFuncSetAttribute(evalKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
+    const int grid = (int) std::max<long long>(1, std::min<long long>((N + groups - 1) / groups, 2LL * m.numSMs));
+    evalKernel<<<grid, groups * 32, smemBytes, stream>>>(v, m.dBlob, N, y, P, ydot, groupDoubles);
+}
+
+void launchReactorInit(const DeviceMech& m, long long N, const double* T, const double* P, const double* Y,
+                       long long ldY, double* y, double* Pout, double* T0, cudaStream_t stream)
+{
+    if (N <= 0) return;
+    const int threads = 128;
+    reactorInitKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, N, T, P, Y, ldY,
+                                                                                      y, Pout, T0);
+}
+
+void launchReactorContents(const DeviceMech& m, long long N, const double* y, double* T, double* Y, long long ldY,
+                           cudaStream_t stream)
+{
+    if (N <= 0) return;
+    const int threads = 128;
+    reactorContentsKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, N, y, T, Y,
+                                                                                          ldY);
+}
+
+} // namespace ctb

@@ -122,7 +122,9 @@ int32_t ctb_kin_newFromTables(const ctb_mech_tables* tables, int32_t device);
 /* Same, from a .ctbm table file written by the extractor (oracle/ref_build/ctb_extract). */
 int32_t ctb_kin_newFromFile(const char* ctbmPath, int32_t device);
 int32_t ctb_kin_del(int32_t handle);
-/* Run subsequent calls on an existing cudaStream_t (NULL = the handle's own stream). */
+/* Run subsequent device-memory calls on an existing cudaStream_t; NULL is the CUDA default stream
+ * (what torch.cuda.current_stream() is unless changed). Until this is called the handle uses a
+ * private non-blocking stream. */
 int32_t ctb_kin_setStream(int32_t handle, void* cudaStream);
 /* Block until all work queued on the handle's stream has finished. */
 int32_t ctb_kin_synchronize(int32_t handle);
@@ -200,6 +202,12 @@ double  ctb_reactornet_time(int32_t handle);                              /* Rea
 /* Contents after the last advance: T[n], Y[n*ldY + k] (ThermoPhase::temperature, massFractions) */
 int32_t ctb_reactornet_getState(int32_t handle, double* T, double* Y, int64_t ldY,
                                 int32_t memspace);
+/* ReactorNet::getState (ReactorNet.cpp:688-695): the solution vectors y[n*(K+1) + i] = [T, n_1..n_K]
+ * (kmol) of every reactor. bufLen >= nReactors*(K+1). */
+int32_t ctb_reactornet_getStateVector(int32_t handle, double* y, int64_t bufLen, int32_t memspace);
+/* ReactorNet::eval (ReactorNet.cpp:617-635; IdealGasConstPressureMoleReactor::eval
+ * IdealGasConstPressureMoleReactor.cpp:52-106) at the current solution vectors: ydot, same layout. */
+int32_t ctb_reactornet_eval(int32_t handle, double* ydot, int64_t bufLen, int32_t memspace);
 /* Per-reactor integrator status: 0 ok, >0 failure code (CTB_STATUS_*). */
 int32_t ctb_reactornet_status(int32_t handle, int64_t len, int32_t* status);
 /* Per-reactor counters, stats[n*CTB_NSTATS + j] (ReactorNet::solverStats,

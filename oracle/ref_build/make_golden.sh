@@ -42,3 +42,8 @@ gg ignite "$D/nDodecane_Reitz.yaml" nDodecane_IG "$G/ignite_nDodecane.ctbm" 16 $
 gg ignite "$D/gri30.yaml" gri30 "$G/substep_gri30.ctbm" 32 $((SEED+4)) CH4 2 O2 N2 1200 2200 1 50 1e-5 0
 gzip -9 -f -n "$G"/rates_*.ctbm "$G"/ddx_*.ctbm "$G"/rhs_*.ctbm "$G"/ignite_*.ctbm "$G"/substep_*.ctbm
 ls -la "$G" "$M"
+# converged references (rtol 1e-11 / atol 1e-18): separate the reference's own integration error from ours
+gg ignite "$D/h2o2.yaml" ohmech "$G/ignite_tight_h2o2.ctbm" 32 $((SEED+0)) H2 0.5 O2 AR 1000 1600 1 20 1e-3 400 1e-11 1e-18
+gg ignite "$D/gri30.yaml" gri30 "$G/ignite_tight_gri30.ctbm" 48 $((SEED+2)) CH4 2 O2 N2 1000 2000 1 50 1e-3 400 1e-11 1e-18
+gg ignite "$D/nDodecane_Reitz.yaml" nDodecane_IG "$G/ignite_tight_nDodecane.ctbm" 16 $((SEED+3)) c12h26 18.5 o2 n2 700 1400 10 50 1e-2 400 1e-11 1e-18
+gzip -9 -f -n "$G"/ignite_tight_*.ctbm
