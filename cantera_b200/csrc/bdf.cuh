@@ -390,7 +390,7 @@ struct Bdf {
     const unsigned char* sm;
     const unsigned char* gm;
     ReactorWork wk;
-    double P, rtol, atolT, atolS;
+    double P, rtol, atolT, atolS, crateFloor;
     // integrator memory (identical in every lane of the group)
     int q, L, qwait, qprime, nst, nstlp;
     bool forceSetup; // the Newton matrix is not kept between advance() calls
@@ -591,7 +591,7 @@ struct Bdf {
                 const double del = sqrt(g.sum(s) / n);
                 g.sync();
                 if (m > 0) crate = fmax(BDF_CRDOWN * crate, del / delp);
-                const double dcon = del * fmin(1.0, crate) / tq[4];
+                const double dcon = del * fmin(1.0, fmax(crate, crateFloor)) / tq[4];
                 if (dcon <= 1.0) {
                     acnrm = (m == 0) ? del : wrms(wk.acor);
                     return 0;

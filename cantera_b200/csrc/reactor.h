@@ -37,6 +37,7 @@ struct ReactorBatch {
     int maxSteps;
     int restart;           // 1: integrator is (re)initialised from y (ReactorNet::setInitialTime)
     double ignDT;          // <= 0: monitor off
+    double crateFloor;     // lower bound of the Newton convergence-rate estimate (see bdf.cuh)
 };
 
 void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stream);

@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(512) advanceKernel(const MechView v, const uns
     Bdf<G> bdf(g, v, sm, gmech, wk);
     bdf.rtol = a.rtol;
     bdf.atolT = a.atol;
+    bdf.crateFloor = a.crateFloor;
 
     for (;;) {
         // ---- next reactor from the queue
