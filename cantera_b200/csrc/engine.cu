@@ -126,6 +126,19 @@ void BatchedGasKinetics::synchronize()
     cudaCheck(cudaStreamSynchronize(stream()), "cudaStreamSynchronize");
 }
 
+// Row-strided copies degrade to one DMA descriptor per row; contiguous batches (ld == width, the
+// common case) go through a single linear copy, which runs at PCIe line rate from pinned memory.
+static void copyRows(double* dst, long long ldDst, const double* src, long long ldSrc, long long width,
+                     long long rows, cudaMemcpyKind kind, cudaStream_t st, const char* what)
+{
+    if (ldDst == width && ldSrc == width) {
+        cudaCheck(cudaMemcpyAsync(dst, src, sizeof(double) * width * rows, kind, st), what);
+    } else {
+        cudaCheck(cudaMemcpy2DAsync(dst, sizeof(double) * ldDst, src, sizeof(double) * ldSrc,
+                                    sizeof(double) * width, rows, kind, st), what);
+    }
+}
+
 static bool anyFull(const RateOutputs& o)
 {
     return o.cdot || o.ddot || o.ropf || o.ropr || o.ropnet || o.kf || o.kc;
@@ -166,7 +179,7 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
     for (double* p : outsR) nR += p != nullptr;
     const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) nW * K + (size_t) nR * R);
     long long chunk = std::max<long long>(1024, std::min<long long>(N, (long long) ((256u << 20) / perState)));
-    chunk = std::min<long long>(chunk, std::max<long long>(1024, (N + 3) / 4));
+    chunk = std::min<long long>(chunk, std::max<long long>(1024, (N + 15) / 16));
     for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
     int b = 0;
     for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
@@ -178,8 +191,7 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
         double* dY = d; d += chunk * K;
         cudaCheck(cudaMemcpyAsync(dT, T + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D T");
         cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
-        cudaCheck(cudaMemcpy2DAsync(dY, sizeof(double) * K, Y + n0 * ldY, sizeof(double) * ldY,
-                                    sizeof(double) * K, n, cudaMemcpyHostToDevice, st), "H2D Y");
+        copyRows(dY, K, Y + n0 * ldY, ldY, K, n, cudaMemcpyHostToDevice, st, "H2D Y");
         RatesArgs a = {};
         a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.ldW = K; a.ldR = R;
         double** slotsW[3] = {&a.wdot, &a.cdot, &a.ddot};
@@ -190,16 +202,12 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
         cudaCheck(cudaGetLastError(), "ratesKernel launch");
         for (int i = 0; i < 3; i++) {
             if (outsW[i]) {
-                cudaCheck(cudaMemcpy2DAsync(outsW[i] + n0 * out.ldW, sizeof(double) * out.ldW, *slotsW[i],
-                                            sizeof(double) * K, sizeof(double) * K, n, cudaMemcpyDeviceToHost, st),
-                          "D2H");
+                copyRows(outsW[i] + n0 * out.ldW, out.ldW, *slotsW[i], K, K, n, cudaMemcpyDeviceToHost, st, "D2H");
             }
         }
         for (int i = 0; i < 5; i++) {
             if (outsR[i]) {
-                cudaCheck(cudaMemcpy2DAsync(outsR[i] + n0 * out.ldR, sizeof(double) * out.ldR, *slotsR[i],
-                                            sizeof(double) * R, sizeof(double) * R, n, cudaMemcpyDeviceToHost, st),
-                          "D2H");
+                copyRows(outsR[i] + n0 * out.ldR, out.ldR, *slotsR[i], R, R, n, cudaMemcpyDeviceToHost, st, "D2H");
             }
         }
     }
@@ -232,7 +240,7 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
     if (memspace != CTB_HOST) throw CtbError("BatchedGasKinetics::jacobian", "memspace must be CTB_HOST or CTB_DEVICE");
     const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) K * K);
     long long chunk = std::max<long long>(256, std::min<long long>(N, (long long) ((256u << 20) / perState)));
-    chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 3) / 4));
+    chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 15) / 16));
     for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
     int b = 0;
     for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
@@ -245,8 +253,7 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
         double* dJ = d;
         cudaCheck(cudaMemcpyAsync(dT, T + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D T");
         cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
-        cudaCheck(cudaMemcpy2DAsync(dY, sizeof(double) * K, Y + n0 * ldY, sizeof(double) * ldY,
-                                    sizeof(double) * K, n, cudaMemcpyHostToDevice, st), "H2D Y");
+        copyRows(dY, K, Y + n0 * ldY, ldY, K, n, cudaMemcpyHostToDevice, st, "H2D Y");
         a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.jac = dJ;
         launchJac(m_dev, a, st);
         cudaCheck(cudaGetLastError(), "jacKernel launch");

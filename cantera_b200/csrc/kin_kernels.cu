@@ -6,9 +6,11 @@
 //
 // Shared memory: [hot mechanism tables (TMA bulk copy)] [mbarrier] [per-group work areas].
 #include "kin_kernels.h"
-#include "rates.cuh"
+#include "rates_thread.cuh"
 
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <type_traits>
 #include <stdexcept>
 #include <string>
@@ -109,6 +111,50 @@ __global__ void __launch_bounds__(512) ratesKernel(const MechView v, const unsig
 }
 
 
+// --------------------------------------------------------------------------- rates, thread/state
+
+//! setState_TPY + updateROP + getNetProductionRates, one THREAD per state (rates_thread.cuh).
+//! Shared memory: [hot mechanism tables][mbarrier][c, g, w : 3 x K x st doubles], st = blockDim+1.
+template <int U>
+__global__ void __launch_bounds__(256, 1) ratesThreadKernel(const MechView v, const unsigned char* __restrict__ gmech,
+                                                            const RatesArgs a, const int st)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + v.hotBytes);
+    tmaStage(smem, gmech, v.hotBytes, bar);
+    const unsigned char* sm = smem;
+    const int K = v.K;
+    double* cAll = reinterpret_cast<double*>(smem + v.hotBytes + 16);
+    double* gAll = cAll + (size_t) K * st;
+    double* wAll = gAll + (size_t) K * st;
+    TArr t;
+    t.c = cAll + threadIdx.x; t.g = gAll + threadIdx.x; t.w = wAll + threadIdx.x; t.st = st;
+    const int NTH = blockDim.x;
+    for (long long base = (long long) blockIdx.x * NTH; base < a.N; base += (long long) gridDim.x * NTH) {
+        const int nb = (int) min((long long) NTH, a.N - base);
+        loadTransposed(cAll, st, a.Y + base * a.ldY, a.ldY, nb, K);
+        const bool valid = (int) threadIdx.x < nb;
+        double T = 1000.0, P = 101325.0;
+        if (valid) {
+            T = a.T[base + threadIdx.x];
+            P = a.P[base + threadIdx.x];
+        }
+        __syncthreads();
+        if (!valid) {
+            for (int k = 0; k < K; k++) t.c[k * st] = 1.0; // idle threads work on a benign state
+        }
+        GasScalars s;
+        double dens;
+        stateFromTPY_T(v, sm, T, P, t, s, dens);
+        thermoT(v, sm, s, t, dens);
+        reactionsT<false, U>(v, sm, s, t);
+        __syncthreads();
+        storeTransposed(a.wdot + base * a.ldW, a.ldW, wAll, st, nb, K);
+        __syncthreads();
+    }
+}
+
+
 // ------------------------------------------------------------------------------------- jacobian
 
 //! One group (a warp, or the whole CTA when CTA_GROUP) per state.
@@ -197,9 +243,45 @@ static void launchRatesT(const DeviceMech& m, const RatesArgs& a, cudaStream_t s
     kern<<<grid, threads, smemBytes, stream>>>(v, m.dBlob, a, workAligned);
 }
 
+//! Threads per CTA of the thread-per-state kernels for this mechanism (0: does not fit).
+int threadKernelThreads(const DeviceMech& m, int arraysPerThread)
+{
+    const MechView& v = m.view;
+    const long long avail = (long long) m.smemOptIn - 1024 - v.hotBytes - 16;
+    long long nth = avail / ((long long) arraysPerThread * v.K * 8) - 1;
+    nth = std::min<long long>(256, (nth / 32) * 32);
+    return nth >= 64 ? (int) nth : 0;
+}
+
+template <int U>
+static void launchRatesThreadT(const DeviceMech& m, const RatesArgs& a, int nth, cudaStream_t stream)
+{
+    const MechView& v = m.view;
+    const int st = nth + 1;
+    const size_t smemBytes = v.hotBytes + 16 + (size_t) 3 * v.K * st * 8;
+    auto kern = ratesThreadKernel<U>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
+    const long long want = (a.N + nth - 1) / nth;
+    const int grid = (int) std::max<long long>(1, std::min<long long>(want, m.numSMs));
+    kern<<<grid, nth, smemBytes, stream>>>(v, m.dBlob, a, st);
+}
+
 void launchRates(const DeviceMech& m, const RatesArgs& a, bool full, cudaStream_t stream)
 {
     if (a.N <= 0) return;
+    // wdot only: one thread per state when the mechanism leaves room for >= 64 states per SM in
+    // shared memory (rates_thread.cuh); otherwise, and for every other getter, a sub-warp group
+    // of 8 lanes per state.
+    if (!full) {
+        const char* force = std::getenv("CTB_RATES_KERNEL");
+        const int nth = threadKernelThreads(m, 3);
+        if (nth > 0 && !(force && std::strcmp(force, "group") == 0)) {
+            const char* u = std::getenv("CTB_RATES_U");
+            if (u && std::atoi(u) == 2) launchRatesThreadT<2>(m, a, nth, stream);
+            else launchRatesThreadT<4>(m, a, nth, stream);
+            return;
+        }
+    }
     // lanes per state: enough states in flight per SM vs. idle lanes in the species loops
     if (full) {
         launchRatesT<8, true>(m, a, stream);

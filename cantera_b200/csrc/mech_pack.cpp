@@ -68,12 +68,40 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         default: throw std::runtime_error("packMechanism: unknown rate type");
         }
     }
+    // fast signature of the thread-per-state kernels (see RunRec)
+    std::vector<int> fcode(R, -1);
+    for (int i = 0; i < R; i++) {
+        if ((cls[i] != CLS_ARR && cls[i] != CLS_ARR_CONST) || (t.rxn_flags[i] & CTB_RXN_THIRD_BODY)) continue;
+        int pat[2] = {-1, -1};
+        std::vector<int> seen;
+        bool ok = true;
+        for (int side = 0; side < 2 && ok; side++) {
+            const int b0 = side ? t.prod_ptr[i] : t.reac_ptr[i], e0 = side ? t.prod_ptr[i + 1] : t.reac_ptr[i + 1];
+            const int32_t* sp = side ? t.prod_species : t.reac_species;
+            const double* st = side ? t.prod_stoich : t.reac_stoich;
+            const double* od = side ? t.prod_stoich : t.reac_order;
+            int molecules;
+            if (e0 == b0 || !simpleSide(e0 - b0, st + b0, od + b0, molecules)) { ok = false; break; }
+            const int n = e0 - b0;
+            if (n == 1 && molecules == 1) pat[side] = PAT_A;
+            else if (n == 2 && molecules == 2) pat[side] = PAT_AB;
+            else if (n == 1 && molecules == 2) pat[side] = PAT_2A;
+            else if (n == 3 && molecules == 3) pat[side] = PAT_ABC;
+            else ok = false;
+            for (int j = b0; j < e0 && ok; j++) {
+                if (std::find(seen.begin(), seen.end(), sp[j]) != seen.end()) ok = false;
+                seen.push_back(sp[j]);
+            }
+        }
+        if (ok) fcode[i] = fastCode(cls[i] == CLS_ARR_CONST, (t.rxn_flags[i] & CTB_RXN_REVERSIBLE) ? 1 : 0, pat[0], pat[1]);
+    }
     pm.perm.resize(R);
     std::iota(pm.perm.begin(), pm.perm.end(), 0);
     // within a class: irreversible first (they skip the equilibrium-constant exp), then
     // third-body flag, then reference order
     std::stable_sort(pm.perm.begin(), pm.perm.end(), [&](int a, int b) {
         if (cls[a] != cls[b]) return cls[a] < cls[b];
+        if (fcode[a] != fcode[b]) return fcode[a] < fcode[b];
         int ra = t.rxn_flags[a] & CTB_RXN_REVERSIBLE, rb = t.rxn_flags[b] & CTB_RXN_REVERSIBLE;
         if (ra != rb) return ra < rb;
         int ta = t.rxn_flags[a] & CTB_RXN_THIRD_BODY, tb = t.rxn_flags[b] & CTB_RXN_THIRD_BODY;
@@ -219,6 +247,14 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         tbTPtr.push_back((int32_t) tbTRxn.size());
     }
 
+    // ---- runs of equal fast signature (general-path reactions form runs of code -1)
+    std::vector<RunRec> runs;
+    for (int e = 0; e < R; e++) {
+        const int code = fcode[pm.perm[e]];
+        if (runs.empty() || runs.back().code != code) runs.push_back(RunRec{e, e + 1, code, 0});
+        else runs.back().end = e + 1;
+    }
+
     // ---- lay out: hot tables first (staged to shared memory), cold tables after
     Blob bl;
     v.o_molwt = bl.put(molwt); v.o_rmolwt = bl.put(rmolwt); v.o_tmid = bl.put(tmid);
@@ -236,6 +272,8 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     v.o_genPtr = bl.put(genPtr); v.o_genSp = bl.put(genSp); v.o_genStoich = bl.put(genStoich);
     v.o_genOrder = bl.put(genOrder);
     v.o_gPtr = bl.put(gPtr); v.o_gEnt = bl.put(gEnt);
+    v.o_runs = bl.put(runs);
+    v.nRuns = (int32_t) runs.size();
     bl.finish();
     v.hotBytes = (uint32_t) bl.data.size();
     v.o_gNu = bl.put(gNu);

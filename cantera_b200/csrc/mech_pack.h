@@ -49,6 +49,25 @@ struct RxnRec {
 static_assert(sizeof(RxnRec) == 16, "RxnRec must be 16 bytes");
 static const uint8_t SIDE_GENERAL = 0xFF;
 
+// Thread-per-state kernels (rates_thread.cuh) walk the execution order as a list of RUNS: maximal
+// segments of reactions that share one "fast signature" (plain Arrhenius, no third body, 1-3
+// distinct unit-stoichiometry molecules per side or one doubled species, no species on both
+// sides) are evaluated by an unrolled, branch-free body; everything else takes the general path.
+struct RunRec {
+    int32_t begin, end; // execution-order range
+    int32_t code;       // fastCode(constK, rev, sideR, sideP) or -1 (general path)
+    int32_t pad;
+};
+static_assert(sizeof(RunRec) == 16, "RunRec must be 16 bytes");
+// side patterns of the fast signature
+enum SidePat : int { PAT_A = 0, PAT_AB = 1, PAT_2A = 2, PAT_ABC = 3, PAT_COUNT = 4 };
+// constK: kf = A (b == 0 and Ea == 0, no exp). Reactant pattern A+B+C is not instantiated.
+inline int fastCode(int constK, int rev, int patR, int patP)
+{
+    if (patR == PAT_ABC) return -1;
+    return (((constK * 2 + rev) * PAT_COUNT) + patR) * PAT_COUNT + patP;
+}
+
 // Species-major gather entry: wdot_k = sum_e nu_e * q[rxn_e]. nu is signed: > 0 for a
 // product-side entry, < 0 for a reactant-side entry (the sign doubles as the role flag for
 // creation / destruction rates). Mechanisms with fractional coefficients read the signed
@@ -106,6 +125,8 @@ struct MechView {
     uint32_t o_gPtr;                        // int32[K+1]
     uint32_t o_gEnt;                        // GatherEnt[nGather]
     uint32_t o_gNu;                         // double[nGather] (only read if hasFractional)
+    uint32_t o_runs;                        // RunRec[nRuns]
+    int32_t nRuns;
     uint32_t bytes;                         // blob size, multiple of 16
     uint32_t hotBytes;                      // prefix staged into shared memory (multiple of 16)
 };
