@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libctb.so")
-SOURCES = ["mech_pack.cpp", "kin_kernels.cu", "engine.cu", "reactor.cu", "reactor_kernels.cu", "ctb_clib.cu"]
+SOURCES = ["mech_pack.cpp", "kin_kernels.cu", "engine.cu", "reactor.cu", "reactor_kernels.cu", "reactor_batch.cu", "ctb_clib.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--fmad=true",
               "-diag-suppress", "177"]

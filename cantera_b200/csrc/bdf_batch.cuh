@@ -1,0 +1,745 @@
+// bdf_batch.cuh — the BDF/Newton controller of BatchReactorNet as a RESUMABLE per-reactor state
+// machine, for the batch-synchronous integrator of reactor_batch.cu.
+//
+// The persistent kernel of reactor_kernels.cu keeps one reactor's whole integrator (Newton matrix
+// included) in shared memory, which bounds an SM to 3-5 reactors in flight. Here the integrator is
+// cut at the points where it needs the chemistry — a right-hand side, or a new Newton matrix — and
+// everything between two such points is ONE invocation of controlSlot() by ONE THREAD:
+//
+//     control (thread/slot)  ->  rhs (thread/slot, rates_thread.cuh)  ->  setup (group/flagged slot)
+//            ^------------------------------------------------------------------------|
+//
+// so that the expensive part (rates) runs as a throughput kernel over all slots at once, and the
+// per-slot data (Nordsieck array, LU factors: ~30 KB for gri30) lives in HBM in a slot-interleaved
+// layout [element][slot]: every access of a warp of the control/rhs kernels is coalesced.
+// A slot that finishes its reactor pulls the next one from a global queue (reactors differ ~10x in
+// step count), so all slots stay busy until the queue is empty.
+//
+// The algorithm is the one of bdf.cuh (same constants, same operation order per reactor: the
+// variable-order variable-step fixed-leading-coefficient BDF of VODE/CVODE with CVODES' controller
+// constants, ext/sundials/src/cvodes/cvodes_impl.h:53-126); only its control flow is inverted.
+// The arithmetic is __host__ __device__: tests/emul runs it on the CPU.
+#pragma once
+
+#include "bdf.cuh"
+
+namespace ctb {
+
+enum BatchPc : int {
+    PC_IDLE = 0,      // no reactor left for this slot
+    PC_NEW = 1,       // take the next reactor from the queue
+    PC_START_F0 = 2,  // f(y0) requested (CVodeInit)
+    PC_HIN = 3,       // f(y0 + hg f0) requested (cvHin)
+    PC_NEWTON = 4,    // f(y) requested inside the Newton iteration (and LU factors if flagged)
+    PC_RESTART1 = 5,  // f(zn0) requested by the order-1 restart after repeated error-test failures
+    // transient states (never stored)
+    X_ADVANCE = 10, X_ATTEMPT = 11, X_NLS_PASS = 12, X_NLS_OK = 13, X_NLS_FAIL = 14, X_STEP_OK = 15,
+    X_START_DONE = 16, X_FINISH = 17
+};
+
+//! Per-slot controller memory.
+struct BatchCtl {
+    int pc, status, q, L, qwait, qprime, nst, nstlp, nst0, ncf, nef, nflag, m, pass, jcur, callSetup,
+        needSing, forceSetup, hinCount, ignPending;
+    int nfe, nsetups, nni, ncfn, netf, pad;
+    long long r;
+    double P, atolS, tn, h, hscale, hprime, eta, etamax, gamma, gammap, gamrat, crate, acnrm, savedTq5, rl1,
+        delp, savedT, dsm, hg, hnew, hub, hlb, h0, tPrev, TPrev, Tign;
+    double tau[BDF_QMAX + 1], tq[BDF_QMAX + 1], l[BDF_QMAX + 1];
+};
+
+//! Slot-interleaved integrator memory: element e of slot s is at arr[e * S + s].
+struct SlotMem {
+    double* zn;    // [6 * n][S] Nordsieck array
+    double* acor;  // [n][S]
+    double* ewt;   // [n][S]
+    double* y;     // [n][S]  state the next right-hand side is evaluated at
+    double* f;     // [n][S]  right-hand side at y
+    double* M;     // [n * n][S] LU factors of I - gamma J, column-major (col * n + row)
+    int* perm;     // [n][S] row permutation of the LU
+    int* sing;     // [S] non-zero: singular Newton matrix
+    BatchCtl* ctl; // [S]
+    int* setupCount;
+    int* setupList; // [S] slots that need a new Newton matrix in this round
+    int* nActive;   // slots that are not idle
+    int S;
+};
+
+CTB_HD long long fetchAddLL(unsigned long long* p)
+{
+#ifdef __CUDA_ARCH__
+    return (long long) atomicAdd(p, 1ULL);
+#else
+    return (long long) ((*p)++);
+#endif
+}
+CTB_HD int fetchAddInt(int* p, int v)
+{
+#ifdef __CUDA_ARCH__
+    return atomicAdd(p, v);
+#else
+    const int o = *p;
+    *p += v;
+    return o;
+#endif
+}
+
+//! One thread advances slot s until it needs a right-hand side (returns with ctl.pc set) or runs
+//! out of reactors. xs: n doubles of scratch with stride xst (shared memory on the device).
+struct BatchBdf {
+    const ReactorBatch& p;
+    const SlotMem& mem;
+    const int n, s;
+    const size_t S;
+    double* const xs;
+    const int xst;
+    BatchCtl c;
+
+    CTB_HD BatchBdf(const ReactorBatch& p_, const SlotMem& m_, int s_, double* xs_, int xst_)
+        : p(p_), mem(m_), n(p_.neq), s(s_), S((size_t) m_.S), xs(xs_), xst(xst_) {}
+
+    CTB_HD double& ZN(int j, int i) const { return mem.zn[((size_t) j * n + i) * S + s]; }
+    CTB_HD double& AC(int i) const { return mem.acor[(size_t) i * S + s]; }
+    CTB_HD double& EW(int i) const { return mem.ewt[(size_t) i * S + s]; }
+    CTB_HD double& Y(int i) const { return mem.y[(size_t) i * S + s]; }
+    CTB_HD double& F(int i) const { return mem.f[(size_t) i * S + s]; }
+
+    CTB_HD void setEwt() const {
+        for (int i = 0; i < n; i++) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
+    }
+    CTB_HD void predict() {
+        c.tn += c.h;
+        const int q = c.q;
+        for (int i = 0; i < n; i++) {
+            double z[BDF_QMAX + 1];
+#pragma unroll
+            for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
+            for (int k = 1; k <= q; k++) {
+#pragma unroll
+                for (int j = BDF_QMAX; j >= 1; j--) if (j >= k && j <= q) z[j - 1] += z[j];
+            }
+#pragma unroll
+            for (int j = 0; j < BDF_QMAX; j++) if (j < q) ZN(j, i) = z[j];
+        }
+    }
+    CTB_HD void restore() {
+        c.tn = c.savedT;
+        const int q = c.q;
+        for (int i = 0; i < n; i++) {
+            double z[BDF_QMAX + 1];
+#pragma unroll
+            for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
+            for (int k = 1; k <= q; k++) {
+#pragma unroll
+                for (int j = BDF_QMAX; j >= 1; j--) if (j >= k && j <= q) z[j - 1] -= z[j];
+            }
+#pragma unroll
+            for (int j = 0; j < BDF_QMAX; j++) if (j < q) ZN(j, i) = z[j];
+        }
+    }
+    CTB_HD void rescale() {
+        double factor = c.eta;
+        for (int j = 1; j <= c.q; j++) {
+            for (int i = 0; i < n; i++) ZN(j, i) *= factor;
+            factor *= c.eta;
+        }
+        c.h = c.hscale * c.eta;
+        c.hscale = c.h;
+    }
+    CTB_HD double wrmsAcor() const {
+        double sum = 0.0;
+        for (int i = 0; i < n; i++) {
+            const double t = AC(i) * EW(i);
+            sum += t * t;
+        }
+        return sqrt(sum / n);
+    }
+
+    // Bdf::setCoefficients of bdf.cuh
+    CTB_HD void setCoefficients() {
+        double* l = c.l;
+        double* tq = c.tq;
+        const double* tau = c.tau;
+        const int q = c.q;
+        const double h = c.h;
+        for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
+        l[0] = l[1] = 1.0;
+        double xi_inv = 1.0, xistar_inv = 1.0, alpha0 = -1.0, alpha0_hat = -1.0, hsum = h;
+        if (q > 1) {
+            for (int j = 2; j < q; j++) {
+                hsum += tau[j - 1];
+                xi_inv = h / hsum;
+                alpha0 -= 1.0 / j;
+                for (int i = j; i >= 1; i--) l[i] += l[i - 1] * xi_inv;
+            }
+            alpha0 -= 1.0 / q;
+            xistar_inv = -l[1] - alpha0;
+            hsum += tau[q - 1];
+            xi_inv = h / hsum;
+            alpha0_hat = -l[1] - xi_inv;
+            for (int i = q; i >= 1; i--) l[i] += l[i - 1] * xistar_inv;
+        }
+        const double A1 = 1.0 - alpha0_hat + alpha0;
+        const double A2 = 1.0 + q * A1;
+        tq[2] = fabs(A1 / (alpha0 * A2));
+        tq[5] = fabs(A2 * xistar_inv / (l[q] * xi_inv));
+        if (c.qwait == 1) {
+            if (q > 1) {
+                const double C = xistar_inv / l[q];
+                const double A3 = alpha0 + 1.0 / q;
+                const double A4 = alpha0_hat + xi_inv;
+                const double Cpinv = (1.0 - A4 + A3) / A3;
+                tq[1] = fabs(C * Cpinv);
+            } else {
+                tq[1] = 1.0;
+            }
+            hsum += tau[q];
+            xi_inv = h / hsum;
+            const double A5 = alpha0 - 1.0 / (q + 1);
+            const double A6 = alpha0_hat - xi_inv;
+            const double Cppinv = (1.0 - A6 + A5) / A2;
+            tq[3] = fabs(Cppinv / (xi_inv * (q + 2) * A5));
+        }
+        tq[4] = BDF_CORTES / tq[2];
+        c.rl1 = 1.0 / l[1];
+        c.gamma = h * c.rl1;
+        if (c.nst == 0) c.gammap = c.gamma;
+        c.gamrat = (c.nst > 0) ? c.gamma / c.gammap : 1.0;
+    }
+
+    // Bdf::adjustOrder of bdf.cuh
+    CTB_HD void adjustOrder(int dq) {
+        double* l = c.l;
+        const double* tau = c.tau;
+        const int q = c.q;
+        if (q == 2 && dq != 1) return;
+        for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
+        if (dq == 1) {
+            l[2] = 1.0;
+            double alpha1 = 1.0, prod = 1.0, xiold = 1.0, alpha0 = -1.0, hsum = c.hscale;
+            if (q > 1) {
+                for (int j = 1; j < q; j++) {
+                    hsum += tau[j + 1];
+                    const double xi = hsum / c.hscale;
+                    prod *= xi;
+                    alpha0 -= 1.0 / (j + 1);
+                    alpha1 += 1.0 / xi;
+                    for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xiold + l[i - 1];
+                    xiold = xi;
+                }
+            }
+            const double A1 = (-alpha0 - alpha1) / prod;
+            for (int i = 0; i < n; i++) {
+                const double zL = A1 * ZN(BDF_QMAX, i);
+                ZN(c.L, i) = zL;
+                for (int j = 2; j <= q; j++) ZN(j, i) += l[j] * zL;
+            }
+        } else {
+            l[2] = 1.0;
+            double hsum = 0.0;
+            for (int j = 1; j <= q - 2; j++) {
+                hsum += tau[j];
+                const double xi = hsum / c.hscale;
+                for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xi + l[i - 1];
+            }
+            for (int i = 0; i < n; i++) {
+                const double zq = ZN(q, i);
+                for (int j = 2; j < q; j++) ZN(j, i) -= l[j] * zq;
+            }
+        }
+    }
+
+    CTB_HD void completeStep() {
+        const int q = c.q;
+        c.nst++;
+        for (int i = q; i >= 2; i--) c.tau[i] = c.tau[i - 1];
+        if (q == 1 && c.nst > 1) c.tau[2] = c.tau[1];
+        c.tau[1] = c.h;
+        const bool saveAcor = (c.qwait - 1 == 1) && (q != BDF_QMAX);
+        for (int i = 0; i < n; i++) {
+            const double a = AC(i);
+            for (int j = 0; j <= q; j++) ZN(j, i) += c.l[j] * a;
+            if (saveAcor) ZN(BDF_QMAX, i) = a;
+        }
+        c.qwait--;
+        if (saveAcor) c.savedTq5 = c.tq[5];
+    }
+    CTB_HD void setEta() {
+        if (c.eta < BDF_THRESH) {
+            c.eta = 1.0;
+            c.hprime = c.h;
+        } else {
+            c.eta = fmin(c.eta, c.etamax);
+            c.hprime = c.h * c.eta;
+        }
+    }
+    CTB_HD void prepareNextStep(double dsm) {
+        const int q = c.q, L = c.L;
+        if (c.etamax == 1.0) {
+            c.qwait = c.qwait > 2 ? c.qwait : 2;
+            c.qprime = q;
+            c.hprime = c.h;
+            c.eta = 1.0;
+            return;
+        }
+        const double etaq = 1.0 / (pow(BDF_BIAS2 * dsm, 1.0 / L) + BDF_ADDON);
+        if (c.qwait != 0) {
+            c.eta = etaq;
+            c.qprime = q;
+            setEta();
+            return;
+        }
+        c.qwait = 2;
+        double etaqm1 = 0.0, etaqp1 = 0.0;
+        if (q > 1) {
+            double sum = 0.0;
+            for (int i = 0; i < n; i++) {
+                const double t = ZN(q, i) * EW(i);
+                sum += t * t;
+            }
+            const double ddn = sqrt(sum / n) * c.tq[1];
+            etaqm1 = 1.0 / (pow(BDF_BIAS1 * ddn, 1.0 / q) + BDF_ADDON);
+        }
+        if (q != BDF_QMAX && c.savedTq5 != 0.0) {
+            const double cquot = (c.tq[5] / c.savedTq5) * pow(c.h / c.tau[2], (double) L);
+            double sum = 0.0;
+            for (int i = 0; i < n; i++) {
+                const double t = (AC(i) - cquot * ZN(BDF_QMAX, i)) * EW(i);
+                sum += t * t;
+            }
+            const double dup = sqrt(sum / n) * c.tq[3];
+            etaqp1 = 1.0 / (pow(BDF_BIAS3 * dup, 1.0 / (L + 1)) + BDF_ADDON);
+        }
+        const double etam = fmax(etaqm1, fmax(etaq, etaqp1));
+        if (etam < BDF_THRESH) {
+            c.eta = 1.0;
+            c.qprime = q;
+            c.hprime = c.h;
+            return;
+        }
+        if (etam == etaq) {
+            c.eta = etaq;
+            c.qprime = q;
+        } else if (etam == etaqm1) {
+            c.eta = etaqm1;
+            c.qprime = q - 1;
+        } else {
+            c.eta = etaqp1;
+            c.qprime = q + 1;
+            for (int i = 0; i < n; i++) ZN(BDF_QMAX, i) = AC(i);
+        }
+        setEta();
+    }
+
+    //! x <- (LU)^-1 x with the slot's factors (luSolve of bdf.cuh, one thread)
+    CTB_HD void solve() const {
+        const double* M = mem.M + s;
+        const int* perm = mem.perm + s;
+        for (int k = 0; k < n; k++) {
+            const int pk = perm[(size_t) k * S];
+            if (pk != k) {
+                const double t = xs[k * xst];
+                xs[k * xst] = xs[pk * xst];
+                xs[pk * xst] = t;
+            }
+        }
+        for (int k = 0; k < n - 1; k++) {
+            const double bk = xs[k * xst];
+            const double* ck = M + (size_t) k * n * S;
+#pragma unroll 4
+            for (int i = k + 1; i < n; i++) xs[i * xst] -= ck[(size_t) i * S] * bk;
+        }
+        for (int k = n - 1; k >= 0; k--) {
+            const double* ck = M + (size_t) k * n * S;
+            const double xk = xs[k * xst] / ck[(size_t) k * S];
+            xs[k * xst] = xk;
+#pragma unroll 4
+            for (int i = 0; i < k; i++) xs[i * xst] -= ck[(size_t) i * S] * xk;
+        }
+    }
+
+    CTB_HD void finish(int status) {
+        const long long r = c.r;
+        double* yg = p.y + r * n;
+        if (status == CTB_STATUS_OK) {
+            // CVodeGetDky, k = 0
+            const double sc = (p.tout - c.tn) / c.h;
+            for (int i = 0; i < n; i++) {
+                double acc = ZN(c.q, i);
+                for (int j = c.q - 1; j >= 0; j--) acc = acc * sc + ZN(j, i);
+                yg[i] = acc;
+            }
+        } else {
+            for (int i = 0; i < n; i++) yg[i] = ZN(0, i);
+        }
+        double* hist = p.hist + r * p.histStride;
+        for (int j = 0; j < 6; j++)
+            for (int i = 0; i < n; i++) hist[j * n + i] = ZN(j, i);
+        double* hs = hist + 6 * n;
+        hs[0] = c.q; hs[1] = c.qwait; hs[2] = c.qprime; hs[3] = c.nst; hs[4] = c.nstlp;
+        hs[5] = c.tn; hs[6] = c.h; hs[7] = c.hscale; hs[8] = c.hprime; hs[9] = c.eta; hs[10] = c.etamax;
+        hs[11] = c.gammap; hs[12] = c.savedTq5; hs[13] = c.crate; hs[14] = c.atolS;
+        for (int i = 0; i <= BDF_QMAX; i++) hs[16 + i] = c.tau[i];
+        for (int i = 0; i <= BDF_QMAX; i++) hs[22 + i] = c.tq[i];
+        p.status[r] = status;
+        long long* st = p.stats + r * CTB_NSTATS;
+        st[STAT_STEPS] += c.nst - c.nst0;
+        st[STAT_RHS] += c.nfe;
+        st[STAT_JAC] += c.nsetups;
+        st[STAT_SETUPS] += c.nsetups;
+        st[STAT_NLITERS] += c.nni;
+        st[STAT_NCFAILS] += c.ncfn;
+        st[STAT_ETFAILS] += c.netf;
+        st[STAT_ORDER] = c.q;
+    }
+
+    //! Returns when the slot waits for a right-hand side (c.pc >= PC_START_F0) or is idle.
+    CTB_HD void run() {
+        c = mem.ctl[s];
+        if (c.pc == PC_IDLE) return;
+        int st = c.pc;
+        int finishStatus = CTB_STATUS_OK;
+        for (;;) {
+            if (st == PC_NEW) {
+                long long r;
+                for (;;) {
+                    r = fetchAddLL(p.counter);
+                    if (r >= p.N) break;
+                    if (p.status[r] == CTB_STATUS_OK || p.restart) break; // failed earlier: stays failed
+                }
+                if (r >= p.N) {
+                    c.pc = PC_IDLE;
+                    fetchAddInt(mem.nActive, -1);
+                    break;
+                }
+                c.r = r;
+                c.P = p.P[r];
+                c.nfe = c.nsetups = c.nni = c.ncfn = c.netf = 0;
+                c.Tign = p.ignDT > 0.0 ? p.T0[r] + p.ignDT : 0.0;
+                c.ignPending = p.ignDT > 0.0 && !(p.tIgn[r] == p.tIgn[r]);
+                c.needSing = 0;
+                if (p.restart) {
+                    const double* yg = p.y + r * n;
+                    double moles = 0.0;
+                    for (int i = 0; i < n; i++) {
+                        const double yi = yg[i];
+                        ZN(0, i) = yi;
+                        Y(i) = yi;
+                        if (i > 0) moles += yi;
+                    }
+                    // MoleReactor::updateDefaultTolerances (MoleReactor.cpp:64-76)
+                    c.atolS = (p.atolUser || !(moles > 0.0)) ? p.atol : p.atol * moles;
+                    c.q = 1; c.L = 2; c.qwait = 2; c.qprime = 1;
+                    c.nst = 0; c.nstlp = 0; c.nst0 = 0; c.forceSetup = 0;
+                    c.etamax = BDF_ETAMX1;
+                    c.eta = 1.0; c.crate = 1.0; c.acnrm = 0.0; c.savedTq5 = 0.0; c.gammap = 0.0; c.gamrat = 1.0;
+                    c.gamma = 0.0; c.rl1 = 1.0;
+                    for (int i = 0; i <= BDF_QMAX; i++) { c.tau[i] = 0.0; c.tq[i] = 0.0; c.l[i] = 0.0; }
+                    c.tn = p.t0;
+                    c.h = c.hscale = c.hprime = 0.0;
+                    setEwt();
+                    c.tPrev = c.tn;
+                    c.TPrev = ZN(0, 0);
+                    c.nfe++;
+                    c.pc = PC_START_F0;
+                    break;
+                }
+                const double* hist = p.hist + r * p.histStride;
+                for (int j = 0; j < 6; j++)
+                    for (int i = 0; i < n; i++) ZN(j, i) = hist[j * n + i];
+                const double* hs = hist + 6 * n;
+                c.q = (int) hs[0]; c.qwait = (int) hs[1]; c.qprime = (int) hs[2]; c.nst = (int) hs[3];
+                c.nstlp = (int) hs[4];
+                c.L = c.q + 1;
+                c.tn = hs[5]; c.h = hs[6]; c.hscale = hs[7]; c.hprime = hs[8]; c.eta = hs[9]; c.etamax = hs[10];
+                c.gammap = hs[11]; c.savedTq5 = hs[12]; c.crate = hs[13]; c.atolS = hs[14];
+                for (int i = 0; i <= BDF_QMAX; i++) c.tau[i] = hs[16 + i];
+                for (int i = 0; i <= BDF_QMAX; i++) c.tq[i] = hs[22 + i];
+                for (int i = 0; i <= BDF_QMAX; i++) c.l[i] = 0.0;
+                c.acnrm = 0.0; c.gamma = c.gammap; c.gamrat = 1.0; c.rl1 = 1.0;
+                c.forceSetup = 1;
+                c.nst0 = c.nst;
+                c.tPrev = c.tn;
+                c.TPrev = ZN(0, 0);
+                st = X_ADVANCE;
+            } else if (st == PC_START_F0) {
+                // cvHin (Bdf::initialStep of bdf.cuh), first part
+                for (int i = 0; i < n; i++) ZN(1, i) = F(i);
+                const double tdist = fabs(p.tout - p.t0);
+                const double tround = 2.220446049250313e-16 * fmax(fabs(p.t0), fabs(p.tout));
+                if (tdist < 2.0 * tround) {
+                    finishStatus = CTB_STATUS_STEP_TOO_SMALL;
+                    st = X_FINISH;
+                    continue;
+                }
+                c.hlb = 100.0 * tround;
+                double hubInv = 0.0;
+                for (int i = 0; i < n; i++) {
+                    const double den = 0.1 * fabs(ZN(0, i)) + 1.0 / EW(i);
+                    hubInv = fmax(hubInv, fabs(ZN(1, i)) / den);
+                }
+                double hub = 0.1 * tdist;
+                if (hub * hubInv > 1.0) hub = 1.0 / hubInv;
+                c.hub = hub;
+                if (hub < c.hlb) {
+                    c.h0 = sqrt(c.hlb * hub);
+                    st = X_START_DONE;
+                    continue;
+                }
+                c.hg = sqrt(c.hlb * hub);
+                c.hnew = c.hg;
+                c.hinCount = 1;
+                for (int i = 0; i < n; i++) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                c.nfe++;
+                c.pc = PC_HIN;
+                break;
+            } else if (st == PC_HIN) {
+                double sum = 0.0;
+                for (int i = 0; i < n; i++) {
+                    const double t = (F(i) - ZN(1, i)) / c.hg * EW(i);
+                    sum += t * t;
+                }
+                const double yddnrm = sqrt(sum / n);
+                bool next;
+                if (!(yddnrm == yddnrm)) { // RHS not finite at the trial point: shrink and retry
+                    c.hg *= 0.2;
+                    c.hnew = c.hg;
+                    next = c.hinCount < 4;
+                } else {
+                    c.hnew = (yddnrm * c.hub * c.hub > 2.0) ? sqrt(2.0 / yddnrm) : sqrt(c.hg * c.hub);
+                    if (c.hinCount == 4) {
+                        next = false;
+                    } else {
+                        const double hrat = c.hnew / c.hg;
+                        if (hrat > 0.5 && hrat < 2.0) {
+                            next = false;
+                        } else if (c.hinCount > 1 && hrat > 2.0) {
+                            c.hnew = c.hg;
+                            next = false;
+                        } else {
+                            c.hg = c.hnew;
+                            next = true;
+                        }
+                    }
+                }
+                if (next) {
+                    c.hinCount++;
+                    for (int i = 0; i < n; i++) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                    c.nfe++;
+                    c.pc = PC_HIN;
+                    break;
+                }
+                double h0 = 0.5 * c.hnew;
+                if (h0 < c.hlb) h0 = c.hlb;
+                if (h0 > c.hub) h0 = c.hub;
+                c.h0 = h0;
+                st = X_START_DONE;
+            } else if (st == X_START_DONE) {
+                if (!(c.h0 > 0.0)) {
+                    finishStatus = CTB_STATUS_STEP_TOO_SMALL;
+                    st = X_FINISH;
+                    continue;
+                }
+                c.h = c.hscale = c.hprime = c.h0;
+                for (int i = 0; i < n; i++) ZN(1, i) *= c.h;
+                st = X_ADVANCE;
+            } else if (st == X_ADVANCE) {
+                if (!(c.tn < p.tout)) {
+                    finishStatus = CTB_STATUS_OK;
+                    st = X_FINISH;
+                    continue;
+                }
+                if (c.nst - c.nst0 >= p.maxSteps) {
+                    finishStatus = CTB_STATUS_TOO_MANY_STEPS;
+                    st = X_FINISH;
+                    continue;
+                }
+                if (c.nst > 0) setEwt();
+                // Bdf::step
+                c.savedT = c.tn;
+                c.ncf = 0; c.nef = 0; c.nflag = NFLAG_FIRST;
+                if (c.nst > 0 && c.hprime != c.h) {
+                    if (c.qprime != c.q) {
+                        adjustOrder(c.qprime - c.q);
+                        c.q = c.qprime;
+                        c.L = c.q + 1;
+                        c.qwait = c.L;
+                    }
+                    rescale();
+                }
+                st = X_ATTEMPT;
+            } else if (st == X_ATTEMPT) {
+                if (!(fabs(c.h) > 1e-290) || !(c.h == c.h)) {
+                    finishStatus = CTB_STATUS_STEP_TOO_SMALL;
+                    st = X_FINISH;
+                    continue;
+                }
+                predict();
+                setCoefficients();
+                // Bdf::nonlinearSolve
+                c.callSetup = (c.nflag != NFLAG_FIRST) || c.nst == 0 || c.nst >= c.nstlp + BDF_MSBP
+                              || fabs(c.gamrat - 1.0) > BDF_DGMAX || c.forceSetup;
+                c.jcur = 0;
+                c.pass = 0;
+                st = X_NLS_PASS;
+            } else if (st == X_NLS_PASS) {
+                for (int i = 0; i < n; i++) {
+                    Y(i) = ZN(0, i);
+                    AC(i) = 0.0;
+                }
+                c.m = 0;
+                c.delp = 0.0;
+                if (c.callSetup) {
+                    const int slot = fetchAddInt(mem.setupCount, 1);
+                    mem.setupList[slot] = s;
+                    c.nfe += 2;
+                    c.nsetups++;
+                    c.callSetup = 0;
+                    c.forceSetup = 0;
+                    c.gamrat = 1.0;
+                    c.crate = 1.0;
+                    c.gammap = c.gamma;
+                    c.nstlp = c.nst;
+                    c.jcur = 1;
+                    c.needSing = 1;
+                } else {
+                    c.nfe++;
+                    c.needSing = 0;
+                }
+                c.pc = PC_NEWTON;
+                break;
+            } else if (st == PC_NEWTON) {
+                if (c.needSing) {
+                    c.needSing = 0;
+                    if (mem.sing[s]) {
+                        st = X_NLS_FAIL;
+                        continue;
+                    }
+                }
+                for (int i = 0; i < n; i++) xs[i * xst] = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
+                solve();
+                c.nni++;
+                const double sc = (c.gamrat != 1.0) ? 2.0 / (1.0 + c.gamrat) : 1.0;
+                double sum = 0.0;
+                for (int i = 0; i < n; i++) {
+                    const double d = xs[i * xst] * sc;
+                    const double t = d * EW(i);
+                    sum += t * t;
+                    const double a = AC(i) + d;
+                    AC(i) = a;
+                    Y(i) = ZN(0, i) + a;
+                }
+                const double del = sqrt(sum / n);
+                if (c.m > 0) c.crate = fmax(BDF_CRDOWN * c.crate, del / c.delp);
+                const double dcon = del * fmin(1.0, fmax(c.crate, p.crateFloor)) / c.tq[4];
+                if (dcon <= 1.0) {
+                    c.acnrm = (c.m == 0) ? del : wrmsAcor();
+                    st = X_NLS_OK;
+                    continue;
+                }
+                c.m++;
+                if (c.m == BDF_MAXCOR || (c.m >= 2 && del > BDF_RDIV * c.delp) || !(del == del)) {
+                    if (c.jcur || c.pass == 1) {
+                        st = X_NLS_FAIL;
+                    } else {
+                        c.callSetup = 1; // the matrix was stale: rebuild it and try once more
+                        c.pass = 1;
+                        st = X_NLS_PASS;
+                    }
+                    continue;
+                }
+                c.delp = del;
+                c.nfe++;
+                c.pc = PC_NEWTON;
+                break;
+            } else if (st == X_NLS_FAIL) {
+                c.ncfn++;
+                restore();
+                c.ncf++;
+                c.etamax = 1.0;
+                if (c.ncf == BDF_MXNCF) {
+                    finishStatus = CTB_STATUS_CONV_FAIL;
+                    st = X_FINISH;
+                    continue;
+                }
+                c.eta = BDF_ETACF;
+                c.nflag = NFLAG_PREV_CONV_FAIL;
+                rescale();
+                st = X_ATTEMPT;
+            } else if (st == X_NLS_OK) {
+                c.dsm = c.acnrm * c.tq[2];
+                if (c.dsm <= 1.0) {
+                    st = X_STEP_OK;
+                    continue;
+                }
+                c.nef++;
+                c.netf++;
+                c.nflag = NFLAG_PREV_ERR_FAIL;
+                restore();
+                if (c.nef == BDF_MXNEF) {
+                    finishStatus = CTB_STATUS_ERR_TEST_FAIL;
+                    st = X_FINISH;
+                    continue;
+                }
+                c.etamax = 1.0;
+                if (c.nef <= BDF_MXNEF1) {
+                    c.eta = 1.0 / (pow(BDF_BIAS2 * c.dsm, 1.0 / c.L) + BDF_ADDON);
+                    c.eta = fmax(BDF_ETAMIN, c.eta);
+                    if (c.nef >= BDF_SMALL_NEF) c.eta = fmin(c.eta, BDF_ETAMXF);
+                    if (!(c.eta == c.eta)) c.eta = BDF_ETAMIN;
+                    rescale();
+                    st = X_ATTEMPT;
+                    continue;
+                }
+                if (c.q > 1) {
+                    c.eta = BDF_ETAMIN;
+                    adjustOrder(-1);
+                    c.L = c.q;
+                    c.q--;
+                    c.qwait = c.L;
+                    rescale();
+                    st = X_ATTEMPT;
+                    continue;
+                }
+                // order 1 and still failing: restart the history from f(tn, zn[0])
+                c.eta = BDF_ETAMIN;
+                c.h *= c.eta;
+                c.hscale = c.h;
+                c.qwait = BDF_LONG_WAIT;
+                for (int i = 0; i < n; i++) Y(i) = ZN(0, i);
+                c.nfe++;
+                c.pc = PC_RESTART1;
+                break;
+            } else if (st == PC_RESTART1) {
+                for (int i = 0; i < n; i++) ZN(1, i) = c.h * F(i);
+                st = X_ATTEMPT;
+            } else if (st == X_STEP_OK) {
+                completeStep();
+                prepareNextStep(c.dsm);
+                c.etamax = BDF_ETAMX2;
+                const double t2 = c.tq[2];
+                for (int i = 0; i < n; i++) AC(i) *= t2;
+                const double Tnow = ZN(0, 0);
+                if (!(Tnow == Tnow)) {
+                    finishStatus = CTB_STATUS_NOT_FINITE;
+                    st = X_FINISH;
+                    continue;
+                }
+                if (c.ignPending && Tnow >= c.Tign) {
+                    // first crossing of T0 + dT, linear in the step (openmp_ignition.cpp:70-73)
+                    p.tIgn[c.r] = c.tPrev + (c.tn - c.tPrev) * (c.Tign - c.TPrev) / (Tnow - c.TPrev);
+                    c.ignPending = 0;
+                }
+                c.tPrev = c.tn;
+                c.TPrev = Tnow;
+                st = X_ADVANCE;
+            } else { // X_FINISH
+                finish(finishStatus);
+                st = PC_NEW;
+            }
+        }
+        mem.ctl[s] = c;
+    }
+};
+
+} // namespace ctb

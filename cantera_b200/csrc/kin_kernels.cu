@@ -269,16 +269,14 @@ static void launchRatesThreadT(const DeviceMech& m, const RatesArgs& a, int nth,
 void launchRates(const DeviceMech& m, const RatesArgs& a, bool full, cudaStream_t stream)
 {
     if (a.N <= 0) return;
-    // wdot only: one thread per state when the mechanism leaves room for >= 64 states per SM in
-    // shared memory (rates_thread.cuh); otherwise, and for every other getter, a sub-warp group
-    // of 8 lanes per state.
+    // Default: a sub-warp group of 8 lanes per state. CTB_RATES_KERNEL=thread selects the
+    // thread-per-state kernel (rates_thread.cuh) for wdot-only calls when the mechanism leaves room
+    // for >= 64 states per SM in shared memory.
     if (!full) {
         const char* force = std::getenv("CTB_RATES_KERNEL");
         const int nth = threadKernelThreads(m, 3);
-        if (nth > 0 && !(force && std::strcmp(force, "group") == 0)) {
-            const char* u = std::getenv("CTB_RATES_U");
-            if (u && std::atoi(u) == 2) launchRatesThreadT<2>(m, a, nth, stream);
-            else launchRatesThreadT<4>(m, a, nth, stream);
+        if (nth > 0 && force && std::strcmp(force, "thread") == 0) {
+            launchRatesThreadT<4>(m, a, nth, stream);
             return;
         }
     }

@@ -274,6 +274,7 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     v.o_gPtr = bl.put(gPtr); v.o_gEnt = bl.put(gEnt);
     v.o_runs = bl.put(runs);
     v.nRuns = (int32_t) runs.size();
+    v.o_view = bl.put(std::vector<unsigned char>(sizeof(MechView), 0)); // patched below
     bl.finish();
     v.hotBytes = (uint32_t) bl.data.size();
     v.o_gNu = bl.put(gNu);
@@ -288,6 +289,7 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     v.nGather = (int32_t) gEnt.size();
     v.hasFractional = fractional ? 1 : 0;
     v.maxChebNT = maxChebNT;
+    std::memcpy(bl.data.data() + v.o_view, &v, sizeof(MechView));
     pm.blob = std::move(bl.data);
     return pm;
 }

@@ -127,6 +127,7 @@ struct MechView {
     uint32_t o_gNu;                         // double[nGather] (only read if hasFractional)
     uint32_t o_runs;                        // RunRec[nRuns]
     int32_t nRuns;
+    uint32_t o_view;                        // a copy of this MechView inside the hot region
     uint32_t bytes;                         // blob size, multiple of 16
     uint32_t hotBytes;                      // prefix staged into shared memory (multiple of 16)
 };

@@ -29,14 +29,60 @@ struct TArr {
     int st;
 };
 
-//! Everything a fast run needs, by value (registers) so that the run bodies can stay separate
-//! functions instead of one giant inlined kernel.
+// The run bodies are separate (noinline) functions: one register allocation each instead of one
+// giant kernel. Across that boundary shared-memory locations travel as 32-bit shared-window
+// addresses (SPtr) and are turned back into pointers with cvta inside the callee, so that the
+// compiler still emits LDS/STS with 32-bit address arithmetic instead of generic loads.
+#ifdef __CUDA_ARCH__
+typedef uint32_t SPtr;
+#define CTB_SP(T, a) (reinterpret_cast<T*>(__cvta_shared_to_generic((size_t) (a))))
+__device__ __forceinline__ SPtr toSPtr(const void* p) { return (SPtr) __cvta_generic_to_shared(p); }
+#else
+typedef const unsigned char* SPtr;
+#define CTB_SP(T, a) (reinterpret_cast<T*>(const_cast<unsigned char*>(a)))
+inline SPtr toSPtr(const void* p) { return static_cast<const unsigned char*>(p); }
+#endif
+
+struct TArrS {
+    SPtr c, g, w;
+    int st;
+};
+CTB_HD TArrS packT(const TArr& a)
+{
+    TArrS r;
+    r.c = toSPtr(a.c); r.g = toSPtr(a.g); r.w = toSPtr(a.w); r.st = a.st;
+    return r;
+}
+CTB_HD TArr unpackT(const TArrS& a)
+{
+    TArr r;
+    r.c = CTB_SP(double, a.c); r.g = CTB_SP(double, a.g); r.w = CTB_SP(double, a.w); r.st = a.st;
+    return r;
+}
+
+//! Everything a fast run needs, by value.
 struct FastCtx {
+    SPtr tA, tb, tE, tmult, tdn, trec;
+    double logT, recipT, rrt, lsc;
+    TArrS a;
+};
+//! Pointer form, rebuilt inside the callee.
+struct FastPtrs {
     const double* tA; const double* tb; const double* tE; const double* tmult; const double* tdn;
     const uint4* trec;
     double logT, recipT, rrt, lsc;
     TArr a;
 };
+CTB_HD FastPtrs unpackCtx(const FastCtx& x)
+{
+    FastPtrs f;
+    f.tA = CTB_SP(const double, x.tA); f.tb = CTB_SP(const double, x.tb); f.tE = CTB_SP(const double, x.tE);
+    f.tmult = CTB_SP(const double, x.tmult); f.tdn = CTB_SP(const double, x.tdn);
+    f.trec = CTB_SP(const uint4, x.trec);
+    f.logT = x.logT; f.recipT = x.recipT; f.rrt = x.rrt; f.lsc = x.lsc;
+    f.a = unpackT(x.a);
+    return f;
+}
 
 CTB_HD void fillScalarsT(const MechView& v, GasScalars& s)
 {
@@ -132,7 +178,7 @@ CTB_HD double mulGathered(const double (&x)[3], double r)
 //! species slots to scatter into. The scatter of the PREVIOUS group (qp, ip) is issued between the
 //! gathers and the exp chains of this one, so that its load-add-store latency hides under them.
 template <int PR, int PP, bool REV, bool CONSTK, bool NEG, int U>
-CTB_HD void fastGroup(const FastCtx& x, const int e, double (&qp)[U], int (&ip)[U][6],
+CTB_HD void fastGroup(const FastPtrs& x, const int e, double (&qp)[U], int (&ip)[U][6],
                                           const bool havePrev)
 {
     constexpr int NR = PatInfo<PR>::N, NP = PatInfo<PP>::N;
@@ -231,8 +277,9 @@ CTB_HD void scatterTail(const TArr& a, const double (&qp)[U], const int (&ip)[U]
 }
 
 template <int PR, int PP, bool REV, bool CONSTK, bool NEG, int U>
-__host__ __device__ __noinline__ void fastRun(const FastCtx x, int e0, int e1)
+__host__ __device__ __noinline__ void fastRun(const FastCtx xs, int e0, int e1)
 {
+    const FastPtrs x = unpackCtx(xs);
     const TArr& a = x.a;
     double qp[U];
     int ip[U][6];
@@ -328,9 +375,12 @@ CTB_HD void sideScatterS(const MechView& v, const unsigned char* sm, int n,
 }
 
 template <bool NEG>
-__host__ __device__ __noinline__ void generalRun(const MechView& v, const unsigned char* sm, int e0, int e1,
-                                        const GasScalars& s, const TArr& a)
+__host__ __device__ __noinline__ void generalRun(const SPtr smS, const uint32_t oView, int e0, int e1,
+                                                 const GasScalars s, const TArrS as)
 {
+    const unsigned char* sm = CTB_SP(const unsigned char, smS);
+    const MechView& v = *reinterpret_cast<const MechView*>(sm + oView); // the blob carries its own view
+    const TArr a = unpackT(as);
     const double* tA = CTB_TAB(double, sm, v.o_A);
     const double* tb = CTB_TAB(double, sm, v.o_b);
     const double* tE = CTB_TAB(double, sm, v.o_EaR);
@@ -412,14 +462,15 @@ CTB_HD void reactionsT(const MechView& v, const unsigned char* sm, const GasScal
                                            const TArr& a)
 {
     FastCtx x;
-    x.tA = CTB_TAB(double, sm, v.o_A);
-    x.tb = CTB_TAB(double, sm, v.o_b);
-    x.tE = CTB_TAB(double, sm, v.o_EaR);
-    x.tmult = CTB_TAB(double, sm, v.o_mult);
-    x.tdn = CTB_TAB(double, sm, v.o_dn);
-    x.trec = CTB_TAB(uint4, sm, v.o_rec);
+    x.tA = toSPtr(sm + v.o_A);
+    x.tb = toSPtr(sm + v.o_b);
+    x.tE = toSPtr(sm + v.o_EaR);
+    x.tmult = toSPtr(sm + v.o_mult);
+    x.tdn = toSPtr(sm + v.o_dn);
+    x.trec = toSPtr(sm + v.o_rec);
     x.logT = s.logT; x.recipT = s.recipT; x.rrt = s.rrt; x.lsc = s.logStandConc;
-    x.a = a;
+    x.a = packT(a);
+    const SPtr smS = toSPtr(sm);
     const RunRec* runs = CTB_TAB(RunRec, sm, v.o_runs);
     for (int i = 0; i < v.nRuns; i++) {
         const int4 rr = *reinterpret_cast<const int4*>(runs + i);
@@ -430,7 +481,7 @@ CTB_HD void reactionsT(const MechView& v, const unsigned char* sm, const GasScal
             CTB_FAST_CASES(1, 0)
             CTB_FAST_CASES(1, 1)
         default:
-            generalRun<NEG>(v, sm, b, e, s, a);
+            generalRun<NEG>(smS, v.o_view, b, e, s, x.a);
         }
     }
 }

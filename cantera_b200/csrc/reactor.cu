@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <limits>
 
 namespace ctb {
@@ -134,8 +135,28 @@ void BatchReactorNet::advance(double t)
     double atolScale = 0.1;
     if (const char* e = std::getenv("CTB_BDF_ATOL_SCALE")) atolScale = std::atof(e);
     b.atol *= atolScale;
-    launchAdvance(m_kin->mech(), b, st);
-    cudaCheck(cudaGetLastError(), "advance launch");
+    // Default: the batch-synchronous integrator (reactor_batch.cu). CTB_BDF_KERNEL=persistent selects
+    // the one-kernel shared-memory integrator (reactor_kernels.cu), which is also the path for
+    // mechanisms too large for the thread-per-reactor kernels.
+    const char* which = std::getenv("CTB_BDF_KERNEL");
+    const long long cap = batchSlotCap(m_kin->mech());
+    if (cap > 0 && !(which && std::strcmp(which, "persistent") == 0)) {
+        long long S = std::min(m_N, cap);
+        if (const char* e = std::getenv("CTB_BDF_SLOTS")) S = std::max(1LL, std::min<long long>(m_N, std::atoll(e)));
+        if (S != m_slots) {
+            m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr));
+            m_slots = S;
+        }
+        try {
+            m_lastRounds = launchAdvanceBatch(m_kin->mech(), b, m_ws.p, S, st);
+        } catch (const std::runtime_error& e) {
+            throw CtbError("BatchReactorNet::advance", e.what());
+        }
+        cudaCheck(cudaGetLastError(), "batch advance");
+    } else {
+        launchAdvance(m_kin->mech(), b, st);
+        cudaCheck(cudaGetLastError(), "advance launch");
+    }
     m_time = t;
     m_restart = false;
 }

@@ -41,6 +41,19 @@ struct ReactorBatch {
 };
 
 void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stream);
+
+// ---- batch-synchronous integrator (reactor_batch.cu)
+//! Byte offsets of the slot-interleaved arrays inside the workspace.
+struct BatchLayout {
+    size_t zn, acor, ewt, y, f, M, perm, sing, ctl, setupList, counters;
+};
+//! Upper bound of useful slots on this device (0: the mechanism does not fit the thread kernels).
+long long batchSlotCap(const DeviceMech& m);
+size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay);
+//! Integrates every reactor of b to b.tout with S slots; synchronous (returns when all reactors are
+//! done). Returns the number of control/rhs/setup rounds.
+long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* workspace, long long S,
+                             cudaStream_t stream);
 //! y <- getState of a reactor holding (T, P, Y) in 1 m^3 (IdealGasConstPressureMoleReactor.cpp:22-30)
 void launchReactorInit(const DeviceMech& m, long long N, const double* T, const double* P, const double* Y,
                        long long ldY, double* y, double* Pout, double* T0, cudaStream_t stream);
@@ -90,7 +103,9 @@ private:
     bool m_haveState = false;
     bool m_restart = true;
     double m_ignDT = 0.0;
-    DevBuf m_y, m_P, m_T0, m_hist, m_tIgn, m_status, m_stats, m_counter, m_io;
+    DevBuf m_y, m_P, m_T0, m_hist, m_tIgn, m_status, m_stats, m_counter, m_io, m_ws;
+    long long m_slots = 0;
+    long long m_lastRounds = 0;
 };
 
 } // namespace ctb
