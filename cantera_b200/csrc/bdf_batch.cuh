@@ -4,14 +4,15 @@
 // The persistent kernel of reactor_kernels.cu keeps one reactor's whole integrator (Newton matrix
 // included) in shared memory, which bounds an SM to 3-5 reactors in flight. Here the integrator is
 // cut at the points where it needs the chemistry — a right-hand side, or a new Newton matrix — and
-// everything between two such points is ONE invocation of controlSlot() by ONE THREAD:
+// everything between two such points is ONE invocation of BatchBdf::run() by ONE WARP:
 //
-//     control (thread/slot)  ->  rhs (thread/slot, rates_thread.cuh)  ->  setup (group/flagged slot)
+//     control (warp/slot)  ->  rhs (thread/slot, rates_thread.cuh)  ->  setup (group/flagged slot)
 //            ^------------------------------------------------------------------------|
 //
 // so that the expensive part (rates) runs as a throughput kernel over all slots at once, and the
-// per-slot data (Nordsieck array, LU factors: ~30 KB for gri30) lives in HBM in a slot-interleaved
-// layout [element][slot]: every access of a warp of the control/rhs kernels is coalesced.
+// per-slot data (Nordsieck array, LU factors: ~30 KB for gri30) lives in HBM, one contiguous block
+// per slot: the lanes of the controlling warp read it with consecutive addresses, and the
+// triangular solves stream the factors column by column (prefetched eight columns ahead).
 // A slot that finishes its reactor pulls the next one from a global queue (reactors differ ~10x in
 // step count), so all slots stay busy until the queue is empty.
 //
@@ -48,15 +49,15 @@ struct BatchCtl {
     double tau[BDF_QMAX + 1], tq[BDF_QMAX + 1], l[BDF_QMAX + 1];
 };
 
-//! Slot-interleaved integrator memory: element e of slot s is at arr[e * S + s].
+//! Slot-major integrator memory: every slot owns contiguous blocks, read by the lanes of its
+//! group with consecutive addresses.
+#define SLOT_VECS 10 // zn[0..5], acor, ewt, y, f
 struct SlotMem {
-    double* zn;    // [6 * n][S] Nordsieck array
-    double* acor;  // [n][S]
-    double* ewt;   // [n][S]
-    double* y;     // [n][S]  state the next right-hand side is evaluated at
-    double* f;     // [n][S]  right-hand side at y
-    double* M;     // [n * n][S] LU factors of I - gamma J, column-major (col * n + row)
-    int* perm;     // [n][S] row permutation of the LU
+    double* vec;   // [S][10][n]: Nordsieck array zn (6 n), acor, ewt, y (state the next right-hand
+                   //             side is evaluated at), f (right-hand side at y)
+    double* M;     // [S][n * n] LU factors of I - gamma J, column-major (col * n + row), with the
+                   //             RECIPROCAL pivots on the diagonal
+    int* perm;     // [S][n] composed row permutation of the LU: (P b)[i] = b[perm[i]]
     int* sing;     // [S] non-zero: singular Newton matrix
     BatchCtl* ctl; // [S]
     int* setupCount;
@@ -84,33 +85,45 @@ CTB_HD int fetchAddInt(int* p, int v)
 #endif
 }
 
-//! One thread advances slot s until it needs a right-hand side (returns with ctl.pc set) or runs
-//! out of reactors. xs: n doubles of scratch with stride xst (shared memory on the device).
+//! The host stand-in for a cooperative group: one "lane" (tests/emul).
+struct Solo {
+    static constexpr int NT = 1;
+    CTB_HD int lane() const { return 0; }
+    CTB_HD void sync() const {}
+    CTB_HD double sum(double x) const { return x; }
+    CTB_HD double max(double x) const { return x; }
+};
+
+//! One cooperative group G (a warp on the device) advances slot s until it needs a right-hand
+//! side (returns with ctl.pc set) or runs out of reactors. Controller scalars are replicated in
+//! every lane (reductions return identical values), vectors are distributed lane-cyclically:
+//! NPL = ceil(n / G::NT) elements per lane.
+template <class G, int NPL>
 struct BatchBdf {
+    const G& g;
     const ReactorBatch& p;
     const SlotMem& mem;
     const int n, s;
-    const size_t S;
-    double* const xs;
-    const int xst;
+    double* const vec; // this slot's vectors
+    double* const xs;  // n doubles of scratch (only used by the one-lane solve)
     BatchCtl c;
 
-    CTB_HD BatchBdf(const ReactorBatch& p_, const SlotMem& m_, int s_, double* xs_, int xst_)
-        : p(p_), mem(m_), n(p_.neq), s(s_), S((size_t) m_.S), xs(xs_), xst(xst_) {}
+    CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, double* xs_)
+        : g(g_), p(p_), mem(m_), n(p_.neq), s(s_), vec(m_.vec + (size_t) s_ * SLOT_VECS * p_.neq), xs(xs_) {}
 
-    CTB_HD double& ZN(int j, int i) const { return mem.zn[((size_t) j * n + i) * S + s]; }
-    CTB_HD double& AC(int i) const { return mem.acor[(size_t) i * S + s]; }
-    CTB_HD double& EW(int i) const { return mem.ewt[(size_t) i * S + s]; }
-    CTB_HD double& Y(int i) const { return mem.y[(size_t) i * S + s]; }
-    CTB_HD double& F(int i) const { return mem.f[(size_t) i * S + s]; }
+    CTB_HD double& ZN(int j, int i) const { return vec[j * n + i]; }
+    CTB_HD double& AC(int i) const { return vec[6 * n + i]; }
+    CTB_HD double& EW(int i) const { return vec[7 * n + i]; }
+    CTB_HD double& Y(int i) const { return vec[8 * n + i]; }
+    CTB_HD double& F(int i) const { return vec[9 * n + i]; }
 
     CTB_HD void setEwt() const {
-        for (int i = 0; i < n; i++) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
+        for (int i = g.lane(); i < n; i += G::NT) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
     }
     CTB_HD void predict() {
         c.tn += c.h;
         const int q = c.q;
-        for (int i = 0; i < n; i++) {
+        for (int i = g.lane(); i < n; i += G::NT) {
             double z[BDF_QMAX + 1];
 #pragma unroll
             for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
@@ -125,7 +138,7 @@ struct BatchBdf {
     CTB_HD void restore() {
         c.tn = c.savedT;
         const int q = c.q;
-        for (int i = 0; i < n; i++) {
+        for (int i = g.lane(); i < n; i += G::NT) {
             double z[BDF_QMAX + 1];
 #pragma unroll
             for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
@@ -140,7 +153,7 @@ struct BatchBdf {
     CTB_HD void rescale() {
         double factor = c.eta;
         for (int j = 1; j <= c.q; j++) {
-            for (int i = 0; i < n; i++) ZN(j, i) *= factor;
+            for (int i = g.lane(); i < n; i += G::NT) ZN(j, i) *= factor;
             factor *= c.eta;
         }
         c.h = c.hscale * c.eta;
@@ -148,11 +161,11 @@ struct BatchBdf {
     }
     CTB_HD double wrmsAcor() const {
         double sum = 0.0;
-        for (int i = 0; i < n; i++) {
+        for (int i = g.lane(); i < n; i += G::NT) {
             const double t = AC(i) * EW(i);
             sum += t * t;
         }
-        return sqrt(sum / n);
+        return sqrt(g.sum(sum) / n);
     }
 
     // Bdf::setCoefficients of bdf.cuh
@@ -229,7 +242,7 @@ struct BatchBdf {
                 }
             }
             const double A1 = (-alpha0 - alpha1) / prod;
-            for (int i = 0; i < n; i++) {
+            for (int i = g.lane(); i < n; i += G::NT) {
                 const double zL = A1 * ZN(BDF_QMAX, i);
                 ZN(c.L, i) = zL;
                 for (int j = 2; j <= q; j++) ZN(j, i) += l[j] * zL;
@@ -242,7 +255,7 @@ struct BatchBdf {
                 const double xi = hsum / c.hscale;
                 for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xi + l[i - 1];
             }
-            for (int i = 0; i < n; i++) {
+            for (int i = g.lane(); i < n; i += G::NT) {
                 const double zq = ZN(q, i);
                 for (int j = 2; j < q; j++) ZN(j, i) -= l[j] * zq;
             }
@@ -256,7 +269,7 @@ struct BatchBdf {
         if (q == 1 && c.nst > 1) c.tau[2] = c.tau[1];
         c.tau[1] = c.h;
         const bool saveAcor = (c.qwait - 1 == 1) && (q != BDF_QMAX);
-        for (int i = 0; i < n; i++) {
+        for (int i = g.lane(); i < n; i += G::NT) {
             const double a = AC(i);
             for (int j = 0; j <= q; j++) ZN(j, i) += c.l[j] * a;
             if (saveAcor) ZN(BDF_QMAX, i) = a;
@@ -293,21 +306,21 @@ struct BatchBdf {
         double etaqm1 = 0.0, etaqp1 = 0.0;
         if (q > 1) {
             double sum = 0.0;
-            for (int i = 0; i < n; i++) {
+            for (int i = g.lane(); i < n; i += G::NT) {
                 const double t = ZN(q, i) * EW(i);
                 sum += t * t;
             }
-            const double ddn = sqrt(sum / n) * c.tq[1];
+            const double ddn = sqrt(g.sum(sum) / n) * c.tq[1];
             etaqm1 = 1.0 / (pow(BDF_BIAS1 * ddn, 1.0 / q) + BDF_ADDON);
         }
         if (q != BDF_QMAX && c.savedTq5 != 0.0) {
             const double cquot = (c.tq[5] / c.savedTq5) * pow(c.h / c.tau[2], (double) L);
             double sum = 0.0;
-            for (int i = 0; i < n; i++) {
+            for (int i = g.lane(); i < n; i += G::NT) {
                 const double t = (AC(i) - cquot * ZN(BDF_QMAX, i)) * EW(i);
                 sum += t * t;
             }
-            const double dup = sqrt(sum / n) * c.tq[3];
+            const double dup = sqrt(g.sum(sum) / n) * c.tq[3];
             etaqp1 = 1.0 / (pow(BDF_BIAS3 * dup, 1.0 / (L + 1)) + BDF_ADDON);
         }
         const double etam = fmax(etaqm1, fmax(etaq, etaqp1));
@@ -326,37 +339,119 @@ struct BatchBdf {
         } else {
             c.eta = etaqp1;
             c.qprime = q + 1;
-            for (int i = 0; i < n; i++) ZN(BDF_QMAX, i) = AC(i);
+            for (int i = g.lane(); i < n; i += G::NT) ZN(BDF_QMAX, i) = AC(i);
         }
         setEta();
     }
 
-    //! x <- (LU)^-1 x with the slot's factors (luSolve of bdf.cuh, one thread)
-    CTB_HD void solve() const {
-        const double* M = mem.M + s;
-        const int* perm = mem.perm + s;
-        for (int k = 0; k < n; k++) {
-            const int pk = perm[(size_t) k * S];
-            if (pk != k) {
-                const double t = xs[k * xst];
-                xs[k * xst] = xs[pk * xst];
-                xs[pk * xst] = t;
-            }
-        }
+    CTB_HD long long bcastLL(long long v) const {
+#ifdef __CUDA_ARCH__
+        if (G::NT > 1) return __shfl_sync(0xffffffffu, v, 0);
+#endif
+        return v;
+    }
+
+    //! One lane: xs[0..n) <- (LU)^-1 P xs (xs has 2 n doubles). The factors carry the reciprocal
+    //! pivots on the diagonal and the composed permutation (luSolve of bdf.cuh otherwise).
+    CTB_HD void solveSerial() const {
+        const double* M = mem.M + (size_t) s * n * n;
+        const int* perm = mem.perm + (size_t) s * n;
+        double* t = xs + n;
+        for (int i = 0; i < n; i++) t[i] = xs[perm[i]];
         for (int k = 0; k < n - 1; k++) {
-            const double bk = xs[k * xst];
-            const double* ck = M + (size_t) k * n * S;
-#pragma unroll 4
-            for (int i = k + 1; i < n; i++) xs[i * xst] -= ck[(size_t) i * S] * bk;
+            const double bk = t[k];
+            const double* ck = M + (size_t) k * n;
+            for (int i = k + 1; i < n; i++) t[i] -= ck[i] * bk;
         }
         for (int k = n - 1; k >= 0; k--) {
-            const double* ck = M + (size_t) k * n * S;
-            const double xk = xs[k * xst] / ck[(size_t) k * S];
-            xs[k * xst] = xk;
-#pragma unroll 4
-            for (int i = 0; i < k; i++) xs[i * xst] -= ck[(size_t) i * S] * xk;
+            const double* ck = M + (size_t) k * n;
+            const double xk = t[k] * ck[k];
+            t[k] = xk;
+            for (int i = 0; i < k; i++) t[i] -= ck[i] * xk;
+        }
+        for (int i = 0; i < n; i++) xs[i] = t[i];
+    }
+
+#ifdef __CUDA_ARCH__
+    //! A warp: element i = lane + 32 j lives in xr[j]. Columns of the factors are streamed from HBM
+    //! (consecutive lanes, consecutive addresses) eight at a time ahead of the dependent chain;
+    //! the pivot element travels by shuffle.
+    __device__ __forceinline__ void solveWarp(double (&xr)[NPL]) const {
+        const double* __restrict__ M = mem.M + (size_t) s * n * n;
+        const int* __restrict__ perm = mem.perm + (size_t) s * n;
+        const int lane = g.lane();
+        constexpr int PF = 8;
+        {
+            double t[NPL];
+#pragma unroll
+            for (int j = 0; j < NPL; j++) {
+                const int i = lane + 32 * j;
+                const int pi = (i < n) ? perm[i] : 0;
+                double val = 0.0;
+#pragma unroll
+                for (int jj = 0; jj < NPL; jj++) {
+                    const double v = __shfl_sync(0xffffffffu, xr[jj], pi & 31);
+                    if ((pi >> 5) == jj) val = v;
+                }
+                t[j] = (i < n) ? val : 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < NPL; j++) xr[j] = t[j];
+        }
+        for (int k0 = 0; k0 < n - 1; k0 += PF) {
+            double col[PF][NPL];
+#pragma unroll
+            for (int u = 0; u < PF; u++) {
+                const int k = k0 + u;
+#pragma unroll
+                for (int j = 0; j < NPL; j++) {
+                    const int i = lane + 32 * j;
+                    col[u][j] = (k < n - 1 && i > k && i < n) ? M[(size_t) k * n + i] : 0.0;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < PF; u++) {
+                const int k = k0 + u;
+                if (k < n - 1) {
+                    double src = xr[0];
+#pragma unroll
+                    for (int jj = 1; jj < NPL; jj++) if ((k >> 5) == jj) src = xr[jj];
+                    const double bk = __shfl_sync(0xffffffffu, src, k & 31);
+#pragma unroll
+                    for (int j = 0; j < NPL; j++) xr[j] -= col[u][j] * bk;
+                }
+            }
+        }
+        for (int k1 = n - 1; k1 >= 0; k1 -= PF) {
+            double col[PF][NPL], dk[PF];
+#pragma unroll
+            for (int u = 0; u < PF; u++) {
+                const int k = k1 - u;
+#pragma unroll
+                for (int j = 0; j < NPL; j++) {
+                    const int i = lane + 32 * j;
+                    col[u][j] = (k >= 0 && i < k) ? M[(size_t) k * n + i] : 0.0;
+                }
+                dk[u] = (k >= 0) ? M[(size_t) k * n + k] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < PF; u++) {
+                const int k = k1 - u;
+                if (k >= 0) {
+                    double src = xr[0];
+#pragma unroll
+                    for (int jj = 1; jj < NPL; jj++) if ((k >> 5) == jj) src = xr[jj];
+                    const double xk = __shfl_sync(0xffffffffu, src, k & 31) * dk[u];
+#pragma unroll
+                    for (int j = 0; j < NPL; j++) {
+                        const int i = lane + 32 * j;
+                        xr[j] = (i == k) ? xk : xr[j] - col[u][j] * xk;
+                    }
+                }
+            }
         }
     }
+#endif
 
     CTB_HD void finish(int status) {
         const long long r = c.r;
@@ -364,17 +459,18 @@ struct BatchBdf {
         if (status == CTB_STATUS_OK) {
             // CVodeGetDky, k = 0
             const double sc = (p.tout - c.tn) / c.h;
-            for (int i = 0; i < n; i++) {
+            for (int i = g.lane(); i < n; i += G::NT) {
                 double acc = ZN(c.q, i);
                 for (int j = c.q - 1; j >= 0; j--) acc = acc * sc + ZN(j, i);
                 yg[i] = acc;
             }
         } else {
-            for (int i = 0; i < n; i++) yg[i] = ZN(0, i);
+            for (int i = g.lane(); i < n; i += G::NT) yg[i] = ZN(0, i);
         }
         double* hist = p.hist + r * p.histStride;
         for (int j = 0; j < 6; j++)
-            for (int i = 0; i < n; i++) hist[j * n + i] = ZN(j, i);
+            for (int i = g.lane(); i < n; i += G::NT) hist[j * n + i] = ZN(j, i);
+        if (g.lane() != 0) return;
         double* hs = hist + 6 * n;
         hs[0] = c.q; hs[1] = c.qwait; hs[2] = c.qprime; hs[3] = c.nst; hs[4] = c.nstlp;
         hs[5] = c.tn; hs[6] = c.h; hs[7] = c.hscale; hs[8] = c.hprime; hs[9] = c.eta; hs[10] = c.etamax;
@@ -401,15 +497,16 @@ struct BatchBdf {
         int finishStatus = CTB_STATUS_OK;
         for (;;) {
             if (st == PC_NEW) {
-                long long r;
+                long long r = 0;
                 for (;;) {
-                    r = fetchAddLL(p.counter);
+                    if (g.lane() == 0) r = fetchAddLL(p.counter);
+                    r = bcastLL(r);
                     if (r >= p.N) break;
                     if (p.status[r] == CTB_STATUS_OK || p.restart) break; // failed earlier: stays failed
                 }
                 if (r >= p.N) {
                     c.pc = PC_IDLE;
-                    fetchAddInt(mem.nActive, -1);
+                    if (g.lane() == 0) fetchAddInt(mem.nActive, -1);
                     break;
                 }
                 c.r = r;
@@ -421,13 +518,14 @@ struct BatchBdf {
                 if (p.restart) {
                     const double* yg = p.y + r * n;
                     double moles = 0.0;
-                    for (int i = 0; i < n; i++) {
+                    for (int i = g.lane(); i < n; i += G::NT) {
                         const double yi = yg[i];
                         ZN(0, i) = yi;
                         Y(i) = yi;
                         if (i > 0) moles += yi;
                     }
                     // MoleReactor::updateDefaultTolerances (MoleReactor.cpp:64-76)
+                    moles = g.sum(moles);
                     c.atolS = (p.atolUser || !(moles > 0.0)) ? p.atol : p.atol * moles;
                     c.q = 1; c.L = 2; c.qwait = 2; c.qprime = 1;
                     c.nst = 0; c.nstlp = 0; c.nst0 = 0; c.forceSetup = 0;
@@ -439,6 +537,7 @@ struct BatchBdf {
                     c.h = c.hscale = c.hprime = 0.0;
                     setEwt();
                     c.tPrev = c.tn;
+                    g.sync();
                     c.TPrev = ZN(0, 0);
                     c.nfe++;
                     c.pc = PC_START_F0;
@@ -446,7 +545,7 @@ struct BatchBdf {
                 }
                 const double* hist = p.hist + r * p.histStride;
                 for (int j = 0; j < 6; j++)
-                    for (int i = 0; i < n; i++) ZN(j, i) = hist[j * n + i];
+                    for (int i = g.lane(); i < n; i += G::NT) ZN(j, i) = hist[j * n + i];
                 const double* hs = hist + 6 * n;
                 c.q = (int) hs[0]; c.qwait = (int) hs[1]; c.qprime = (int) hs[2]; c.nst = (int) hs[3];
                 c.nstlp = (int) hs[4];
@@ -460,11 +559,12 @@ struct BatchBdf {
                 c.forceSetup = 1;
                 c.nst0 = c.nst;
                 c.tPrev = c.tn;
+                g.sync();
                 c.TPrev = ZN(0, 0);
                 st = X_ADVANCE;
             } else if (st == PC_START_F0) {
                 // cvHin (Bdf::initialStep of bdf.cuh), first part
-                for (int i = 0; i < n; i++) ZN(1, i) = F(i);
+                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) = F(i);
                 const double tdist = fabs(p.tout - p.t0);
                 const double tround = 2.220446049250313e-16 * fmax(fabs(p.t0), fabs(p.tout));
                 if (tdist < 2.0 * tround) {
@@ -474,10 +574,11 @@ struct BatchBdf {
                 }
                 c.hlb = 100.0 * tround;
                 double hubInv = 0.0;
-                for (int i = 0; i < n; i++) {
+                for (int i = g.lane(); i < n; i += G::NT) {
                     const double den = 0.1 * fabs(ZN(0, i)) + 1.0 / EW(i);
                     hubInv = fmax(hubInv, fabs(ZN(1, i)) / den);
                 }
+                hubInv = g.max(hubInv);
                 double hub = 0.1 * tdist;
                 if (hub * hubInv > 1.0) hub = 1.0 / hubInv;
                 c.hub = hub;
@@ -489,17 +590,17 @@ struct BatchBdf {
                 c.hg = sqrt(c.hlb * hub);
                 c.hnew = c.hg;
                 c.hinCount = 1;
-                for (int i = 0; i < n; i++) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                for (int i = g.lane(); i < n; i += G::NT) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
                 c.nfe++;
                 c.pc = PC_HIN;
                 break;
             } else if (st == PC_HIN) {
                 double sum = 0.0;
-                for (int i = 0; i < n; i++) {
+                for (int i = g.lane(); i < n; i += G::NT) {
                     const double t = (F(i) - ZN(1, i)) / c.hg * EW(i);
                     sum += t * t;
                 }
-                const double yddnrm = sqrt(sum / n);
+                const double yddnrm = sqrt(g.sum(sum) / n);
                 bool next;
                 if (!(yddnrm == yddnrm)) { // RHS not finite at the trial point: shrink and retry
                     c.hg *= 0.2;
@@ -524,7 +625,7 @@ struct BatchBdf {
                 }
                 if (next) {
                     c.hinCount++;
-                    for (int i = 0; i < n; i++) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                    for (int i = g.lane(); i < n; i += G::NT) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
                     c.nfe++;
                     c.pc = PC_HIN;
                     break;
@@ -541,7 +642,7 @@ struct BatchBdf {
                     continue;
                 }
                 c.h = c.hscale = c.hprime = c.h0;
-                for (int i = 0; i < n; i++) ZN(1, i) *= c.h;
+                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) *= c.h;
                 st = X_ADVANCE;
             } else if (st == X_ADVANCE) {
                 if (!(c.tn < p.tout)) {
@@ -583,15 +684,14 @@ struct BatchBdf {
                 c.pass = 0;
                 st = X_NLS_PASS;
             } else if (st == X_NLS_PASS) {
-                for (int i = 0; i < n; i++) {
+                for (int i = g.lane(); i < n; i += G::NT) {
                     Y(i) = ZN(0, i);
                     AC(i) = 0.0;
                 }
                 c.m = 0;
                 c.delp = 0.0;
                 if (c.callSetup) {
-                    const int slot = fetchAddInt(mem.setupCount, 1);
-                    mem.setupList[slot] = s;
+                    if (g.lane() == 0) mem.setupList[fetchAddInt(mem.setupCount, 1)] = s;
                     c.nfe += 2;
                     c.nsetups++;
                     c.callSetup = 0;
@@ -616,20 +716,45 @@ struct BatchBdf {
                         continue;
                     }
                 }
-                for (int i = 0; i < n; i++) xs[i * xst] = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
-                solve();
                 c.nni++;
                 const double sc = (c.gamrat != 1.0) ? 2.0 / (1.0 + c.gamrat) : 1.0;
                 double sum = 0.0;
-                for (int i = 0; i < n; i++) {
-                    const double d = xs[i * xst] * sc;
-                    const double t = d * EW(i);
-                    sum += t * t;
-                    const double a = AC(i) + d;
-                    AC(i) = a;
-                    Y(i) = ZN(0, i) + a;
+#ifdef __CUDA_ARCH__
+                if (G::NT > 1) {
+                    double xr[NPL];
+#pragma unroll
+                    for (int j = 0; j < NPL; j++) {
+                        const int i = g.lane() + G::NT * j;
+                        xr[j] = (i < n) ? c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i)) : 0.0;
+                    }
+                    solveWarp(xr);
+#pragma unroll
+                    for (int j = 0; j < NPL; j++) {
+                        const int i = g.lane() + G::NT * j;
+                        if (i < n) {
+                            const double d = xr[j] * sc;
+                            const double t = d * EW(i);
+                            sum += t * t;
+                            const double a = AC(i) + d;
+                            AC(i) = a;
+                            Y(i) = ZN(0, i) + a;
+                        }
+                    }
+                } else
+#endif
+                {
+                    for (int i = 0; i < n; i++) xs[i] = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
+                    solveSerial();
+                    for (int i = 0; i < n; i++) {
+                        const double d = xs[i] * sc;
+                        const double t = d * EW(i);
+                        sum += t * t;
+                        const double a = AC(i) + d;
+                        AC(i) = a;
+                        Y(i) = ZN(0, i) + a;
+                    }
                 }
-                const double del = sqrt(sum / n);
+                const double del = sqrt(g.sum(sum) / n);
                 if (c.m > 0) c.crate = fmax(BDF_CRDOWN * c.crate, del / c.delp);
                 const double dcon = del * fmin(1.0, fmax(c.crate, p.crateFloor)) / c.tq[4];
                 if (dcon <= 1.0) {
@@ -706,19 +831,20 @@ struct BatchBdf {
                 c.h *= c.eta;
                 c.hscale = c.h;
                 c.qwait = BDF_LONG_WAIT;
-                for (int i = 0; i < n; i++) Y(i) = ZN(0, i);
+                for (int i = g.lane(); i < n; i += G::NT) Y(i) = ZN(0, i);
                 c.nfe++;
                 c.pc = PC_RESTART1;
                 break;
             } else if (st == PC_RESTART1) {
-                for (int i = 0; i < n; i++) ZN(1, i) = c.h * F(i);
+                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) = c.h * F(i);
                 st = X_ATTEMPT;
             } else if (st == X_STEP_OK) {
                 completeStep();
                 prepareNextStep(c.dsm);
                 c.etamax = BDF_ETAMX2;
                 const double t2 = c.tq[2];
-                for (int i = 0; i < n; i++) AC(i) *= t2;
+                for (int i = g.lane(); i < n; i += G::NT) AC(i) *= t2;
+                g.sync();
                 const double Tnow = ZN(0, 0);
                 if (!(Tnow == Tnow)) {
                     finishStatus = CTB_STATUS_NOT_FINITE;
@@ -727,7 +853,7 @@ struct BatchBdf {
                 }
                 if (c.ignPending && Tnow >= c.Tign) {
                     // first crossing of T0 + dT, linear in the step (openmp_ignition.cpp:70-73)
-                    p.tIgn[c.r] = c.tPrev + (c.tn - c.tPrev) * (c.Tign - c.TPrev) / (Tnow - c.TPrev);
+                    if (g.lane() == 0) p.tIgn[c.r] = c.tPrev + (c.tn - c.tPrev) * (c.Tign - c.TPrev) / (Tnow - c.TPrev);
                     c.ignPending = 0;
                 }
                 c.tPrev = c.tn;
@@ -738,7 +864,7 @@ struct BatchBdf {
                 st = PC_NEW;
             }
         }
-        mem.ctl[s] = c;
+        if (g.lane() == 0) mem.ctl[s] = c;
     }
 };
 

@@ -45,7 +45,7 @@ void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stre
 // ---- batch-synchronous integrator (reactor_batch.cu)
 //! Byte offsets of the slot-interleaved arrays inside the workspace.
 struct BatchLayout {
-    size_t zn, acor, ewt, y, f, M, perm, sing, ctl, setupList, counters;
+    size_t vec, M, perm, sing, ctl, setupList, counters;
 };
 //! Upper bound of useful slots on this device (0: the mechanism does not fit the thread kernels).
 long long batchSlotCap(const DeviceMech& m);

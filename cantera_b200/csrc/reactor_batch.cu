@@ -1,12 +1,12 @@
 // reactor_batch.cu — the batch-synchronous integrator of BatchReactorNet (SURVEY.md §8 rows
 // a12-a14): rounds of three kernels over a pool of SLOTS,
 //
-//   batchControlKernel  one thread per slot: the resumable BDF/Newton controller of bdf_batch.cuh
+//   batchControlKernel  one warp per slot: the resumable BDF/Newton controller of bdf_batch.cuh
 //                       (triangular solves stream the slot's LU factors from HBM, coalesced)
 //   batchRhsKernel      one thread per slot: reactor right-hand side at the requested state
 //                       (reactor_thread.cuh; species arrays in shared memory, [species][thread])
 //   batchSetupKernel    one cooperative group per FLAGGED slot: analytic Newton matrix + dense LU
-//                       in shared memory (bdf.cuh), factors written back slot-interleaved
+//                       in shared memory (bdf.cuh), factors written back to the slot's block
 //
 // with the per-slot integrator memory in HBM. Compared with the persistent one-kernel integrator
 // of reactor_kernels.cu (3-5 reactors per SM, everything in shared memory) this keeps thousands of
@@ -32,13 +32,13 @@ __global__ void batchInitKernel(SlotMem mem)
     if (s == 0) *mem.nActive = mem.S;
 }
 
+template <int NPL>
 __global__ void __launch_bounds__(128) batchControlKernel(const ReactorBatch b, const SlotMem mem)
 {
-    extern __shared__ __align__(16) unsigned char smem[];
-    double* xs = reinterpret_cast<double*>(smem);
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= mem.S) return;
-    BatchBdf bdf(b, mem, s, xs + threadIdx.x, blockDim.x);
+    const SubWarp<32> g;
+    BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, nullptr);
     bdf.run();
 }
 
@@ -57,18 +57,28 @@ __global__ void __launch_bounds__(256, 1) batchRhsKernel(const MechView v, const
     t.g = cAll + (size_t) K * st + threadIdx.x;
     t.w = cAll + (size_t) 2 * K * st + threadIdx.x;
     t.st = st;
-    const size_t S = (size_t) mem.S;
+    double* wAll = cAll + (size_t) 2 * K * st;
+    const size_t ld = (size_t) SLOT_VECS * neq;
     for (int base = blockIdx.x * blockDim.x; base < mem.S; base += gridDim.x * blockDim.x) {
+        const int nb = min((int) blockDim.x, mem.S - base);
+        const double* yb = mem.vec + (size_t) base * ld + 8 * neq; // y block of the first slot
+        // moles n_k of the CTA's slots -> c[k][thread] (coalesced rows, transposed through smem)
+        loadTransposed(cAll, st, yb + 1, (long long) ld, nb, K);
         const int s = base + threadIdx.x;
-        if (s >= mem.S) continue;
-        const BatchCtl* c = mem.ctl + s;
-        if (c->pc == PC_IDLE) continue;
-        const double P = c->P;
-        const double T = mem.y[s];
-        for (int k = 0; k < K; k++) t.c[k * st] = mem.y[(size_t) (1 + k) * S + s];
-        const double Tdot = reactorRhsT<U>(v, sm, T, P, t);
-        mem.f[s] = Tdot;
-        for (int k = 0; k < K; k++) mem.f[(size_t) (1 + k) * S + s] = t.w[k * st];
+        const bool valid = (int) threadIdx.x < nb && mem.ctl[s].pc != PC_IDLE;
+        double T = 1000.0, P = 101325.0;
+        if (valid) {
+            T = yb[(size_t) threadIdx.x * ld];
+            P = mem.ctl[s].P;
+        }
+        __syncthreads();
+        double Tdot = 0.0;
+        if (valid) Tdot = reactorRhsT<U>(v, sm, T, P, t);
+        __syncthreads();
+        double* fb = mem.vec + (size_t) base * ld + 9 * neq;
+        storeTransposed(fb + 1, (long long) ld, wAll, st, nb, K);
+        if (valid) fb[(size_t) threadIdx.x * ld] = Tdot;
+        __syncthreads();
     }
 }
 
@@ -89,24 +99,36 @@ __global__ void __launch_bounds__(512) batchSetupKernel(const MechView v, const 
     const G g(base, 1 + gInCta);
     const ReactorWork wk = carveWork(base + 16, v.K, v.R);
     const int n = wk.n, ldm = wk.ldm;
-    const size_t S = (size_t) mem.S;
     const int count = *mem.setupCount;
     for (int e = blockIdx.x * groups + gInCta; e < count; e += gridDim.x * groups) {
         const int s = mem.setupList[e];
         const double P = mem.ctl[s].P;
         const double gamma = mem.ctl[s].gamma;
-        for (int i = g.lane(); i < n; i += NT) wk.y[i] = mem.y[(size_t) i * S + s];
+        const double* ys = mem.vec + ((size_t) s * SLOT_VECS + 8) * n;
+        for (int i = g.lane(); i < n; i += NT) wk.y[i] = ys[i];
         g.sync();
         buildNewtonMatrix(g, v, sm, gmech, wk, P, gamma);
         const int fail = luFactor(g, wk);
         g.sync();
-        for (int col = 0; col < n; col++) {
-            const double* src = wk.M + (size_t) col * ldm;
-            double* dst = mem.M + (size_t) col * n * S + s;
-            for (int i = g.lane(); i < n; i += NT) dst[(size_t) i * S] = src[i];
+        // factors to the slot's block: column-major n x n, reciprocal pivots on the diagonal
+        double* dstM = mem.M + (size_t) s * n * n;
+        for (int e2 = g.lane(); e2 < n * n; e2 += NT) {
+            const int col = e2 / n, row = e2 - col * n;
+            const double a = wk.M[(size_t) col * ldm + row];
+            dstM[e2] = (row == col) ? 1.0 / a : a;
         }
-        for (int i = g.lane(); i < n; i += NT) mem.perm[(size_t) i * S + s] = wk.perm[i];
-        if (g.lane() == 0) mem.sing[s] = fail;
+        // composed permutation: (P b)[i] = b[id[i]] after the recorded sequence of row swaps
+        int* id = reinterpret_cast<int*>(wk.tmp);
+        if (g.lane() == 0) {
+            for (int i = 0; i < n; i++) id[i] = i;
+            for (int k = 0; k < n; k++) {
+                const int pk = wk.perm[k];
+                if (pk != k) { const int t = id[k]; id[k] = id[pk]; id[pk] = t; }
+            }
+            mem.sing[s] = fail;
+        }
+        g.sync();
+        for (int i = g.lane(); i < n; i += NT) mem.perm[(size_t) s * n + i] = id[i];
         g.sync();
     }
 }
@@ -165,11 +187,7 @@ size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay)
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t) 255; return o; };
     BatchLayout l;
-    l.zn = take(sizeof(double) * 6 * neq * S);
-    l.acor = take(sizeof(double) * neq * S);
-    l.ewt = take(sizeof(double) * neq * S);
-    l.y = take(sizeof(double) * neq * S);
-    l.f = take(sizeof(double) * neq * S);
+    l.vec = take(sizeof(double) * SLOT_VECS * neq * S);
     l.M = take(sizeof(double) * (size_t) neq * neq * S);
     l.perm = take(sizeof(int) * neq * S);
     l.sing = take(sizeof(int) * S);
@@ -189,11 +207,7 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     batchWorkspaceBytes(n, S, &l);
     unsigned char* w = static_cast<unsigned char*>(workspace);
     SlotMem mem = {};
-    mem.zn = reinterpret_cast<double*>(w + l.zn);
-    mem.acor = reinterpret_cast<double*>(w + l.acor);
-    mem.ewt = reinterpret_cast<double*>(w + l.ewt);
-    mem.y = reinterpret_cast<double*>(w + l.y);
-    mem.f = reinterpret_cast<double*>(w + l.f);
+    mem.vec = reinterpret_cast<double*>(w + l.vec);
     mem.M = reinterpret_cast<double*>(w + l.M);
     mem.perm = reinterpret_cast<int*>(w + l.perm);
     mem.sing = reinterpret_cast<int*>(w + l.sing);
@@ -212,9 +226,9 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     const int rhsGrid = (int) std::max<long long>(1, std::min<long long>((S + nth - 1) / nth, m.numSMs));
 
     const int ctlThreads = 128;
-    const size_t ctlSmem = (size_t) n * ctlThreads * 8;
-    cudaFuncSetAttribute(batchControlKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctlSmem);
-    const int ctlGrid = (int) ((S + ctlThreads - 1) / ctlThreads);
+    const int ctlGrid = (int) ((S + ctlThreads / 32 - 1) / (ctlThreads / 32));
+    const int npl = (n + 31) / 32;
+    if (npl > 4) throw std::runtime_error("more than 128 equations per reactor: use the persistent integrator");
 
     batchInitKernel<<<(unsigned) ((S + 255) / 256), 256, 0, stream>>>(mem);
     long long rounds = 0;
@@ -222,7 +236,12 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     int active = 1;
     while (rounds < maxRounds) {
         cudaMemsetAsync(mem.setupCount, 0, sizeof(int), stream);
-        batchControlKernel<<<ctlGrid, ctlThreads, ctlSmem, stream>>>(b, mem);
+        switch (npl) {
+        case 1: batchControlKernel<1><<<ctlGrid, ctlThreads, 0, stream>>>(b, mem); break;
+        case 2: batchControlKernel<2><<<ctlGrid, ctlThreads, 0, stream>>>(b, mem); break;
+        case 3: batchControlKernel<3><<<ctlGrid, ctlThreads, 0, stream>>>(b, mem); break;
+        default: batchControlKernel<4><<<ctlGrid, ctlThreads, 0, stream>>>(b, mem); break;
+        }
         rhsKern<<<rhsGrid, nth, rhsSmem, stream>>>(v, m.dBlob, mem, n, st);
         launchSetup(m, mem, stream);
         rounds++;

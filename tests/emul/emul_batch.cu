@@ -70,35 +70,35 @@ int main(int argc, char** argv)
     b.counter = &counter; b.t0 = 0.0; b.tout = th[0]; b.rtol = 1e-9; b.atol = 1e-15 * 0.1; b.atolUser = 0;
     b.maxSteps = 20000; b.restart = 1; b.ignDT = th[1]; b.crateFloor = 0.0;
 
-    std::vector<double> zn(6 * n * S), acor(n * S), ewt(n * S), ys(n * S), fs(n * S), M((size_t) n * n * S);
+    std::vector<double> vec((size_t) SLOT_VECS * n * S), M((size_t) n * n * S);
     std::vector<int> perm(n * S), sing(S, 0), setupList(S);
     std::vector<BatchCtl> ctl(S);
     for (auto& c : ctl) { std::memset(&c, 0, sizeof(c)); c.pc = PC_NEW; }
     int setupCount = 0, nActive = S;
     SlotMem mem = {};
-    mem.zn = zn.data(); mem.acor = acor.data(); mem.ewt = ewt.data(); mem.y = ys.data(); mem.f = fs.data();
+    mem.vec = vec.data();
     mem.M = M.data(); mem.perm = perm.data(); mem.sing = sing.data(); mem.ctl = ctl.data();
     mem.setupCount = &setupCount; mem.setupList = setupList.data(); mem.nActive = &nActive; mem.S = S;
 
-    std::vector<double> xs(n), yy(n), f0(n), f1(n), J((size_t) n * n);
+    const Solo solo;
+    std::vector<double> xs(2 * n), yy(n), f0(n), f1(n), J((size_t) n * n);
     long long rounds = 0;
     for (;; rounds++) {
         setupCount = 0;
         for (int s = 0; s < S; s++) {
-            BatchBdf bdf(b, mem, s, xs.data(), 1);
+            BatchBdf<Solo, 1> bdf(solo, b, mem, s, xs.data());
             bdf.run();
         }
         if (nActive == 0) break;
         for (int s = 0; s < S; s++) {
             if (ctl[s].pc == PC_IDLE) continue;
-            for (int i = 0; i < n; i++) yy[i] = ys[(size_t) i * S + s];
-            hostRhs(pm, ctl[s].P, yy.data(), f0.data());
-            for (int i = 0; i < n; i++) fs[(size_t) i * S + s] = f0[i];
+            double* sv = vec.data() + (size_t) s * SLOT_VECS * n;
+            hostRhs(pm, ctl[s].P, sv + 8 * n, sv + 9 * n);
         }
         for (int e = 0; e < setupCount; e++) {
             const int s = setupList[e];
             const double gamma = ctl[s].gamma;
-            for (int i = 0; i < n; i++) yy[i] = ys[(size_t) i * S + s];
+            for (int i = 0; i < n; i++) yy[i] = vec[((size_t) s * SLOT_VECS + 8) * n + i];
             hostRhs(pm, ctl[s].P, yy.data(), f0.data());
             double ntot = 0.0;
             for (int i = 1; i < n; i++) ntot += yy[i];
@@ -112,11 +112,13 @@ int main(int argc, char** argv)
                 for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * (f1[i] - f0[i]) / d;
             }
             int fail = 0;
+            std::vector<int> id(n);
+            for (int i = 0; i < n; i++) id[i] = i;
             for (int k = 0; k < n; k++) {
                 int pv = k;
                 double best = std::fabs(J[(size_t) k * n + k]);
                 for (int i = k + 1; i < n; i++) if (std::fabs(J[(size_t) k * n + i]) > best) { best = std::fabs(J[(size_t) k * n + i]); pv = i; }
-                perm[(size_t) k * S + s] = pv;
+                std::swap(id[k], id[pv]);
                 if (!(best > 0.0)) { fail = 1; continue; }
                 if (pv != k) for (int j = 0; j < n; j++) std::swap(J[(size_t) j * n + k], J[(size_t) j * n + pv]);
                 const double rp = 1.0 / J[(size_t) k * n + k];
@@ -127,7 +129,10 @@ int main(int argc, char** argv)
                 }
             }
             sing[s] = fail;
-            for (size_t e2 = 0; e2 < (size_t) n * n; e2++) M[e2 * S + s] = J[e2];
+            for (int i = 0; i < n; i++) perm[(size_t) s * n + i] = id[i];
+            for (int col = 0; col < n; col++)
+                for (int row = 0; row < n; row++)
+                    M[(size_t) s * n * n + (size_t) col * n + row] = (row == col) ? 1.0 / J[(size_t) col * n + row] : J[(size_t) col * n + row];
         }
     }
     std::fprintf(stderr, "rounds %lld\n", rounds);
