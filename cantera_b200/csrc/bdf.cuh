@@ -181,11 +181,24 @@ __device__ __forceinline__ void reactorRhs(const G& g, const MechView& v, const 
     const double cp_mole = CTB_GAS_CONSTANT * (mmw * sumq);
     const double totalCp = totalMass * (cp_mole / mmw);
     double mcpdTdt = 0.0;
-    for (int k = g.lane(); k < K; k += G::NT) {
-        const double wdot = gatherSpecies<0>(v, sm, gm, k, wk.q, nullptr);
-        const double hk = wk.hrt[k] * s.RT;
-        mcpdTdt -= wdot * hk * vol;
-        ydot[1 + k] = wdot * vol;
+    if (G::NT == 8) {
+        // balanced deal of the species to the 8 lanes (mech_pack.h o_gl8*)
+        const int32_t* lp = CTB_TAB(int32_t, sm, v.o_gl8Ptr);
+        const uint16_t* ls = CTB_TAB(uint16_t, sm, v.o_gl8Sp);
+        for (int i = lp[g.lane()]; i < lp[g.lane() + 1]; i++) {
+            const int k = ls[i];
+            const double wdot = gatherSpecies<0>(v, sm, gm, k, wk.q, nullptr);
+            const double hk = wk.hrt[k] * s.RT;
+            mcpdTdt -= wdot * hk * vol;
+            ydot[1 + k] = wdot * vol;
+        }
+    } else {
+        for (int k = g.lane(); k < K; k += G::NT) {
+            const double wdot = gatherSpecies<0>(v, sm, gm, k, wk.q, nullptr);
+            const double hk = wk.hrt[k] * s.RT;
+            mcpdTdt -= wdot * hk * vol;
+            ydot[1 + k] = wdot * vol;
+        }
     }
     mcpdTdt = g.sum(mcpdTdt);
     const double Tdot = mcpdTdt / totalCp;
@@ -209,13 +222,23 @@ __device__ __forceinline__ void reactorRhs(const G& g, const MechView& v, const 
 template <class G>
 __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v, const unsigned char* sm,
                                                   const unsigned char* gm, const ReactorWork& wk, double P,
-                                                  double gamma)
+                                                  double gamma, long long* prof = nullptr)
 {
     const int K = v.K, n = wk.n, ldm = wk.ldm;
     RhsAux aux;
+    long long tk = prof ? clock64() : 0;
+    auto tick = [&](int slot) {
+        if (prof) {
+            const long long t = clock64();
+            if (g.lane() == 0) atomicAdd(reinterpret_cast<unsigned long long*>(prof + slot), (unsigned long long) (t - tk));
+            tk = t;
+        }
+    };
     reactorRhs<G, true>(g, v, sm, gm, wk, P, wk.y, wk.f, aux);
+    tick(0);
     double* A = wk.M + ldm + 1; // species block, A[j*ldm + k]
-    jacobianCi(g, v, sm, gm, wk.c, wk.rfn, wk.rkc, wk.concm, wk.dk, wk.w, wk.D, A, ldm, 1.0, false, false);
+    jacobianCi<G, true>(g, v, sm, gm, wk.c, wk.rfn, wk.rkc, wk.concm, wk.dk, wk.w, wk.D, A, ldm, 1.0, false, false);
+    tick(1);
     // add_k = wdot_k / ctot - sum_l A_kl X_l
     const double rctot = 1.0 / aux.ctot;
     const double rN = 1.0 / (aux.vol * aux.ctot);
@@ -238,6 +261,7 @@ __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v,
         wk.M[(size_t) (1 + j) * ldm] = -(acc * aux.RT + aux.Tdot * (CTB_GAS_CONSTANT * wk.cpr[j])) * rC;
     }
     g.sync();
+    tick(2);
     // temperature column
     const double T = wk.y[0];
     const double dT = T * 1.4901161193847656e-08; // sqrt(DBL_EPSILON)
@@ -247,6 +271,7 @@ __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v,
     g.sync();
     RhsAux aux2;
     reactorRhs<G, false>(g, v, sm, gm, wk, P, wk.b, wk.tmp, aux2);
+    tick(3);
     const double rdT = 1.0 / dT;
     for (int i = g.lane(); i < n; i += G::NT) wk.M[i] = (wk.tmp[i] - wk.f[i]) * rdT;
     g.sync();
@@ -255,6 +280,7 @@ __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v,
         for (int i = g.lane(); i < n; i += G::NT) col[i] = (i == j ? 1.0 : 0.0) - gamma * col[i];
     }
     g.sync();
+    tick(4);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -42,29 +42,50 @@ enum BatchPc : int {
 struct BatchCtl {
     int pc, status, q, L, qwait, qprime, nst, nstlp, nst0, ncf, nef, nflag, m, pass, jcur, callSetup,
         needSing, forceSetup, hinCount, ignPending;
-    int nfe, nsetups, nni, ncfn, netf, pad;
+    int nfe, nsetups, nni, ncfn, netf;
+    int sing; // written by the setup kernel: non-zero = singular Newton matrix
     long long r;
     double P, atolS, tn, h, hscale, hprime, eta, etamax, gamma, gammap, gamrat, crate, acnrm, savedTq5, rl1,
         delp, savedT, dsm, hg, hnew, hub, hlb, h0, tPrev, TPrev, Tign;
     double tau[BDF_QMAX + 1], tq[BDF_QMAX + 1], l[BDF_QMAX + 1];
 };
 
-//! Slot-major integrator memory: every slot owns contiguous blocks, read by the lanes of its
-//! group with consecutive addresses.
-#define SLOT_VECS 10 // zn[0..5], acor, ewt, y, f
+//! Slot-major integrator memory. Every slot owns ONE contiguous, 128-byte aligned block
+//!     [ BatchCtl | vec: zn[0..5], acor, ewt, y, f (10 n doubles) | perm (n ints) | M (n*n doubles) ]
+//! so that the control kernel can bring a whole slot into shared memory with a single TMA bulk copy
+//! and write the mutable prefix (ctl + vec) back with another. y = state the next right-hand side
+//! is evaluated at, f = right-hand side at y; M = LU factors of I - gamma J, column-major
+//! (col * n + row) with the RECIPROCAL pivots on the diagonal; perm = composed row permutation,
+//! (P b)[i] = b[perm[i]].
+#define SLOT_VECS 10
 struct SlotMem {
-    double* vec;   // [S][10][n]: Nordsieck array zn (6 n), acor, ewt, y (state the next right-hand
-                   //             side is evaluated at), f (right-hand side at y)
-    double* M;     // [S][n * n] LU factors of I - gamma J, column-major (col * n + row), with the
-                   //             RECIPROCAL pivots on the diagonal
-    int* perm;     // [S][n] composed row permutation of the LU: (P b)[i] = b[perm[i]]
-    int* sing;     // [S] non-zero: singular Newton matrix
-    BatchCtl* ctl; // [S]
+    unsigned char* slots;
+    unsigned long long slotBytes; // multiple of 128
+    unsigned int oVec, oPerm, oM; // byte offsets inside a slot block (multiples of 16)
+    int* pc;        // [S] copy of ctl.pc (lets kernels skip idle slots without touching the block)
     int* setupCount;
     int* setupList; // [S] slots that need a new Newton matrix in this round
     int* nActive;   // slots that are not idle
-    int S;
+    long long* prof; // optional cycle counters of the setup kernel phases (CTB_PROFILE), or null
+    int S, n;
+    CTB_HD unsigned char* block(int s) const { return slots + (size_t) s * slotBytes; }
+    CTB_HD BatchCtl* ctl(int s) const { return reinterpret_cast<BatchCtl*>(block(s)); }
+    CTB_HD double* vec(int s) const { return reinterpret_cast<double*>(block(s) + oVec); }
+    CTB_HD int* perm(int s) const { return reinterpret_cast<int*>(block(s) + oPerm); }
+    CTB_HD double* M(int s) const { return reinterpret_cast<double*>(block(s) + oM); }
 };
+
+//! Fills the layout fields of a SlotMem for n equations; returns the bytes per slot.
+inline unsigned long long slotLayout(int n, SlotMem& m)
+{
+    auto up = [](unsigned long long x, unsigned long long a) { return (x + a - 1) / a * a; };
+    m.n = n;
+    m.oVec = (unsigned int) up(sizeof(BatchCtl), 16);
+    m.oPerm = m.oVec + (unsigned int) (sizeof(double) * SLOT_VECS * n);
+    m.oM = m.oPerm + (unsigned int) up(sizeof(int) * n, 16);
+    m.slotBytes = up(m.oM + sizeof(double) * (unsigned long long) n * n, 128);
+    return m.slotBytes;
+}
 
 CTB_HD long long fetchAddLL(unsigned long long* p)
 {
@@ -104,12 +125,18 @@ struct BatchBdf {
     const ReactorBatch& p;
     const SlotMem& mem;
     const int n, s;
-    double* const vec; // this slot's vectors
-    double* const xs;  // n doubles of scratch (only used by the one-lane solve)
+    BatchCtl* const ctlPtr;  // this slot's block: in HBM, or its shared-memory copy
+    double* const vec;
+    const int* const permPtr;
+    const double* const MPtr;
+    double* const xs;  // 2 n doubles of scratch (only used by the one-lane solve)
     BatchCtl c;
 
-    CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, double* xs_)
-        : g(g_), p(p_), mem(m_), n(p_.neq), s(s_), vec(m_.vec + (size_t) s_ * SLOT_VECS * p_.neq), xs(xs_) {}
+    //! blk: the slot's block (SlotMem layout) wherever it currently lives
+    CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, unsigned char* blk, double* xs_)
+        : g(g_), p(p_), mem(m_), n(p_.neq), s(s_), ctlPtr(reinterpret_cast<BatchCtl*>(blk)),
+          vec(reinterpret_cast<double*>(blk + m_.oVec)), permPtr(reinterpret_cast<const int*>(blk + m_.oPerm)),
+          MPtr(reinterpret_cast<const double*>(blk + m_.oM)), xs(xs_) {}
 
     CTB_HD double& ZN(int j, int i) const { return vec[j * n + i]; }
     CTB_HD double& AC(int i) const { return vec[6 * n + i]; }
@@ -168,37 +195,55 @@ struct BatchBdf {
         return sqrt(g.sum(sum) / n);
     }
 
+    // The history arrays tau, tq, l are only ever indexed with compile-time constants below (fully
+    // unrolled, predicated loops; get6 for the few run-time indices), so that the whole controller
+    // memory lives in registers: a per-lane copy in local memory would not fit the L1 that the
+    // slot buffers leave.
+    CTB_HD static double get6(const double (&a)[BDF_QMAX + 1], int i) {
+        double r = a[0];
+#pragma unroll
+        for (int k = 1; k <= BDF_QMAX; k++) if (i == k) r = a[k];
+        return r;
+    }
+
     // Bdf::setCoefficients of bdf.cuh
     CTB_HD void setCoefficients() {
-        double* l = c.l;
-        double* tq = c.tq;
-        const double* tau = c.tau;
+        double (&l)[BDF_QMAX + 1] = c.l;
+        double (&tq)[BDF_QMAX + 1] = c.tq;
+        const double (&tau)[BDF_QMAX + 1] = c.tau;
         const int q = c.q;
         const double h = c.h;
+#pragma unroll
         for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
         l[0] = l[1] = 1.0;
         double xi_inv = 1.0, xistar_inv = 1.0, alpha0 = -1.0, alpha0_hat = -1.0, hsum = h;
         if (q > 1) {
-            for (int j = 2; j < q; j++) {
-                hsum += tau[j - 1];
-                xi_inv = h / hsum;
-                alpha0 -= 1.0 / j;
-                for (int i = j; i >= 1; i--) l[i] += l[i - 1] * xi_inv;
+#pragma unroll
+            for (int j = 2; j < BDF_QMAX; j++) {
+                if (j < q) {
+                    hsum += tau[j - 1];
+                    xi_inv = h / hsum;
+                    alpha0 -= 1.0 / j;
+#pragma unroll
+                    for (int i = BDF_QMAX; i >= 1; i--) if (i <= j) l[i] += l[i - 1] * xi_inv;
+                }
             }
             alpha0 -= 1.0 / q;
             xistar_inv = -l[1] - alpha0;
-            hsum += tau[q - 1];
+            hsum += get6(tau, q - 1);
             xi_inv = h / hsum;
             alpha0_hat = -l[1] - xi_inv;
-            for (int i = q; i >= 1; i--) l[i] += l[i - 1] * xistar_inv;
+#pragma unroll
+            for (int i = BDF_QMAX; i >= 1; i--) if (i <= q) l[i] += l[i - 1] * xistar_inv;
         }
+        const double lq = get6(l, q);
         const double A1 = 1.0 - alpha0_hat + alpha0;
         const double A2 = 1.0 + q * A1;
         tq[2] = fabs(A1 / (alpha0 * A2));
-        tq[5] = fabs(A2 * xistar_inv / (l[q] * xi_inv));
+        tq[5] = fabs(A2 * xistar_inv / (lq * xi_inv));
         if (c.qwait == 1) {
             if (q > 1) {
-                const double C = xistar_inv / l[q];
+                const double C = xistar_inv / lq;
                 const double A3 = alpha0 + 1.0 / q;
                 const double A4 = alpha0_hat + xi_inv;
                 const double Cpinv = (1.0 - A4 + A3) / A3;
@@ -206,7 +251,7 @@ struct BatchBdf {
             } else {
                 tq[1] = 1.0;
             }
-            hsum += tau[q];
+            hsum += get6(tau, q);
             xi_inv = h / hsum;
             const double A5 = alpha0 - 1.0 / (q + 1);
             const double A6 = alpha0_hat - xi_inv;
@@ -222,42 +267,53 @@ struct BatchBdf {
 
     // Bdf::adjustOrder of bdf.cuh
     CTB_HD void adjustOrder(int dq) {
-        double* l = c.l;
-        const double* tau = c.tau;
+        double (&l)[BDF_QMAX + 1] = c.l;
+        const double (&tau)[BDF_QMAX + 1] = c.tau;
         const int q = c.q;
         if (q == 2 && dq != 1) return;
+#pragma unroll
         for (int i = 0; i <= BDF_QMAX; i++) l[i] = 0.0;
         if (dq == 1) {
             l[2] = 1.0;
             double alpha1 = 1.0, prod = 1.0, xiold = 1.0, alpha0 = -1.0, hsum = c.hscale;
             if (q > 1) {
-                for (int j = 1; j < q; j++) {
-                    hsum += tau[j + 1];
-                    const double xi = hsum / c.hscale;
-                    prod *= xi;
-                    alpha0 -= 1.0 / (j + 1);
-                    alpha1 += 1.0 / xi;
-                    for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xiold + l[i - 1];
-                    xiold = xi;
+#pragma unroll
+                for (int j = 1; j < BDF_QMAX - 1; j++) { // q + 1 <= BDF_QMAX here, so j <= q - 1 <= 3
+                    if (j < q) {
+                        hsum += tau[j + 1];
+                        const double xi = hsum / c.hscale;
+                        prod *= xi;
+                        alpha0 -= 1.0 / (j + 1);
+                        alpha1 += 1.0 / xi;
+#pragma unroll
+                        for (int i = BDF_QMAX; i >= 2; i--) if (i <= j + 2) l[i] = l[i] * xiold + l[i - 1];
+                        xiold = xi;
+                    }
                 }
             }
             const double A1 = (-alpha0 - alpha1) / prod;
             for (int i = g.lane(); i < n; i += G::NT) {
                 const double zL = A1 * ZN(BDF_QMAX, i);
                 ZN(c.L, i) = zL;
-                for (int j = 2; j <= q; j++) ZN(j, i) += l[j] * zL;
+#pragma unroll
+                for (int j = 2; j <= BDF_QMAX; j++) if (j <= q) ZN(j, i) += l[j] * zL;
             }
         } else {
             l[2] = 1.0;
             double hsum = 0.0;
-            for (int j = 1; j <= q - 2; j++) {
-                hsum += tau[j];
-                const double xi = hsum / c.hscale;
-                for (int i = j + 2; i >= 2; i--) l[i] = l[i] * xi + l[i - 1];
+#pragma unroll
+            for (int j = 1; j <= BDF_QMAX - 2; j++) {
+                if (j <= q - 2) {
+                    hsum += tau[j];
+                    const double xi = hsum / c.hscale;
+#pragma unroll
+                    for (int i = BDF_QMAX; i >= 2; i--) if (i <= j + 2) l[i] = l[i] * xi + l[i - 1];
+                }
             }
             for (int i = g.lane(); i < n; i += G::NT) {
                 const double zq = ZN(q, i);
-                for (int j = 2; j < q; j++) ZN(j, i) -= l[j] * zq;
+#pragma unroll
+                for (int j = 2; j < BDF_QMAX; j++) if (j < q) ZN(j, i) -= l[j] * zq;
             }
         }
     }
@@ -265,13 +321,15 @@ struct BatchBdf {
     CTB_HD void completeStep() {
         const int q = c.q;
         c.nst++;
-        for (int i = q; i >= 2; i--) c.tau[i] = c.tau[i - 1];
+#pragma unroll
+        for (int i = BDF_QMAX; i >= 2; i--) if (i <= q) c.tau[i] = c.tau[i - 1];
         if (q == 1 && c.nst > 1) c.tau[2] = c.tau[1];
         c.tau[1] = c.h;
         const bool saveAcor = (c.qwait - 1 == 1) && (q != BDF_QMAX);
         for (int i = g.lane(); i < n; i += G::NT) {
             const double a = AC(i);
-            for (int j = 0; j <= q; j++) ZN(j, i) += c.l[j] * a;
+#pragma unroll
+            for (int j = 0; j <= BDF_QMAX; j++) if (j <= q) ZN(j, i) += c.l[j] * a;
             if (saveAcor) ZN(BDF_QMAX, i) = a;
         }
         c.qwait--;
@@ -354,8 +412,8 @@ struct BatchBdf {
     //! One lane: xs[0..n) <- (LU)^-1 P xs (xs has 2 n doubles). The factors carry the reciprocal
     //! pivots on the diagonal and the composed permutation (luSolve of bdf.cuh otherwise).
     CTB_HD void solveSerial() const {
-        const double* M = mem.M + (size_t) s * n * n;
-        const int* perm = mem.perm + (size_t) s * n;
+        const double* M = MPtr;
+        const int* perm = permPtr;
         double* t = xs + n;
         for (int i = 0; i < n; i++) t[i] = xs[perm[i]];
         for (int k = 0; k < n - 1; k++) {
@@ -377,8 +435,8 @@ struct BatchBdf {
     //! (consecutive lanes, consecutive addresses) eight at a time ahead of the dependent chain;
     //! the pivot element travels by shuffle.
     __device__ __forceinline__ void solveWarp(double (&xr)[NPL]) const {
-        const double* __restrict__ M = mem.M + (size_t) s * n * n;
-        const int* __restrict__ perm = mem.perm + (size_t) s * n;
+        const double* __restrict__ M = MPtr;
+        const int* __restrict__ perm = permPtr;
         const int lane = g.lane();
         constexpr int PF = 8;
         {
@@ -475,8 +533,8 @@ struct BatchBdf {
         hs[0] = c.q; hs[1] = c.qwait; hs[2] = c.qprime; hs[3] = c.nst; hs[4] = c.nstlp;
         hs[5] = c.tn; hs[6] = c.h; hs[7] = c.hscale; hs[8] = c.hprime; hs[9] = c.eta; hs[10] = c.etamax;
         hs[11] = c.gammap; hs[12] = c.savedTq5; hs[13] = c.crate; hs[14] = c.atolS;
-        for (int i = 0; i <= BDF_QMAX; i++) hs[16 + i] = c.tau[i];
-        for (int i = 0; i <= BDF_QMAX; i++) hs[22 + i] = c.tq[i];
+#pragma unroll
+        for (int i = 0; i <= BDF_QMAX; i++) { hs[16 + i] = c.tau[i]; hs[22 + i] = c.tq[i]; }
         p.status[r] = status;
         long long* st = p.stats + r * CTB_NSTATS;
         st[STAT_STEPS] += c.nst - c.nst0;
@@ -491,7 +549,7 @@ struct BatchBdf {
 
     //! Returns when the slot waits for a right-hand side (c.pc >= PC_START_F0) or is idle.
     CTB_HD void run() {
-        c = mem.ctl[s];
+        c = *ctlPtr;
         if (c.pc == PC_IDLE) return;
         int st = c.pc;
         int finishStatus = CTB_STATUS_OK;
@@ -532,6 +590,7 @@ struct BatchBdf {
                     c.etamax = BDF_ETAMX1;
                     c.eta = 1.0; c.crate = 1.0; c.acnrm = 0.0; c.savedTq5 = 0.0; c.gammap = 0.0; c.gamrat = 1.0;
                     c.gamma = 0.0; c.rl1 = 1.0;
+#pragma unroll
                     for (int i = 0; i <= BDF_QMAX; i++) { c.tau[i] = 0.0; c.tq[i] = 0.0; c.l[i] = 0.0; }
                     c.tn = p.t0;
                     c.h = c.hscale = c.hprime = 0.0;
@@ -552,9 +611,8 @@ struct BatchBdf {
                 c.L = c.q + 1;
                 c.tn = hs[5]; c.h = hs[6]; c.hscale = hs[7]; c.hprime = hs[8]; c.eta = hs[9]; c.etamax = hs[10];
                 c.gammap = hs[11]; c.savedTq5 = hs[12]; c.crate = hs[13]; c.atolS = hs[14];
-                for (int i = 0; i <= BDF_QMAX; i++) c.tau[i] = hs[16 + i];
-                for (int i = 0; i <= BDF_QMAX; i++) c.tq[i] = hs[22 + i];
-                for (int i = 0; i <= BDF_QMAX; i++) c.l[i] = 0.0;
+#pragma unroll
+                for (int i = 0; i <= BDF_QMAX; i++) { c.tau[i] = hs[16 + i]; c.tq[i] = hs[22 + i]; c.l[i] = 0.0; }
                 c.acnrm = 0.0; c.gamma = c.gammap; c.gamrat = 1.0; c.rl1 = 1.0;
                 c.forceSetup = 1;
                 c.nst0 = c.nst;
@@ -711,7 +769,7 @@ struct BatchBdf {
             } else if (st == PC_NEWTON) {
                 if (c.needSing) {
                     c.needSing = 0;
-                    if (mem.sing[s]) {
+                    if (c.sing) {
                         st = X_NLS_FAIL;
                         continue;
                     }
@@ -864,7 +922,10 @@ struct BatchBdf {
                 st = PC_NEW;
             }
         }
-        if (g.lane() == 0) mem.ctl[s] = c;
+        if (g.lane() == 0) {
+            *ctlPtr = c;
+            mem.pc[s] = c.pc;
+        }
     }
 };
 

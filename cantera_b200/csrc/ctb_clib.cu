@@ -1,6 +1,7 @@
 // ctb_clib.cu — the extern "C" boundary (include/ctb_clib.h). Handle cabinets, error stack and
 // exception translation follow the reference's CLib conventions
 // (interfaces/clib/src/Cabinet.h:57-206, interfaces/clib/src/clib_utils.h:34-56).
+#include <algorithm>
 #include "../../include/ctb_clib.h"
 #include "engine.h"
 #include "reactor.h"
@@ -88,7 +89,54 @@ int32_t copyString(const std::string& s, int32_t bufLen, char* buf)
 
 } // namespace
 
+namespace {
+// 8 independent DFMA chains per thread, fully unrolled: the FP64 pipe is the only limiter.
+__global__ void __launch_bounds__(256) dfmaPeakKernel(double* out, int iters, double a, double b)
+{
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    const double r = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (r == 123.456) out[0] = r; // never true: keeps the chains alive
+}
+} // namespace
+
 extern "C" {
+
+double ctb_fp64PeakTflops(int32_t device)
+{
+    return guarded<double>(CTB_DERR, CTB_DERR, [&] {
+        cudaCheck(cudaSetDevice(device), "cudaSetDevice");
+        int sms = 0;
+        cudaCheck(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
+        double* d = nullptr;
+        cudaCheck(cudaMalloc(&d, 64), "cudaMalloc");
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        const int iters = 4096, grid = sms * 8, threads = 256;
+        double best = 0.0;
+        for (int rep = 0; rep < 4; rep++) {
+            cudaEventRecord(e0);
+            dfmaPeakKernel<<<grid, threads>>>(d, iters, 0.999999, 1e-9);
+            cudaEventRecord(e1);
+            cudaCheck(cudaEventSynchronize(e1), "dfmaPeakKernel");
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            const double flop = 2.0 * 8 * 16 * (double) iters * (double) grid * threads;
+            if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaFree(d);
+        return best;
+    });
+}
 
 int32_t ctb_getError(int32_t bufLen, char* buf) { return copyString(t_lastError, bufLen, buf); }
 

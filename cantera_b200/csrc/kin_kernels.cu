@@ -70,8 +70,18 @@ __global__ void __launch_bounds__(512) ratesKernel(const MechView v, const unsig
         if (valid) {
             if (!FULL) {
                 double* out = a.wdot + n * a.ldW;
-                for (int k = g.lane(); k < K; k += NT) {
-                    out[k] = gatherSpecies<0>(v, sm, gmech, k, ropf, nullptr);
+                if (NT == 8) {
+                    // balanced deal of the species to the 8 lanes (mech_pack.h o_gl8*)
+                    const int32_t* lp = CTB_TAB(int32_t, sm, v.o_gl8Ptr);
+                    const uint16_t* ls = CTB_TAB(uint16_t, sm, v.o_gl8Sp);
+                    for (int i = lp[g.lane()]; i < lp[g.lane() + 1]; i++) {
+                        const int k = ls[i];
+                        out[k] = gatherSpecies<0>(v, sm, gmech, k, ropf, nullptr);
+                    }
+                } else {
+                    for (int k = g.lane(); k < K; k += NT) {
+                        out[k] = gatherSpecies<0>(v, sm, gmech, k, ropf, nullptr);
+                    }
                 }
             } else {
                 for (int e = g.lane(); e < R; e += NT) {

@@ -233,6 +233,28 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         gPtr.push_back((int32_t) gEnt.size());
     }
 
+    // ---- balanced deal of the gather lists to 8 lanes (a few radicals own most entries: H has 145
+    // of gri30's 1245, so "species k to lane k mod 8" leaves seven lanes idle most of the time)
+    std::vector<int32_t> gl8Ptr(9, 0);
+    std::vector<uint16_t> gl8Sp;
+    {
+        std::vector<int> order(K);
+        std::iota(order.begin(), order.end(), 0);
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lists[a].size() > lists[b].size(); });
+        std::vector<std::vector<int>> lane(8);
+        long long load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int k : order) {
+            int best = 0;
+            for (int l = 1; l < 8; l++) if (load[l] < load[best]) best = l;
+            lane[best].push_back(k);
+            load[best] += (long long) lists[k].size() + 2; // + per-species overhead
+        }
+        for (int l = 0; l < 8; l++) {
+            for (int k : lane[l]) gl8Sp.push_back((uint16_t) k);
+            gl8Ptr[l + 1] = (int32_t) gl8Sp.size();
+        }
+    }
+
     // ---- transposed third-body efficiencies
     std::vector<std::vector<std::pair<int, double>>> tbT(K);
     for (int e = 0; e < R; e++) {
@@ -272,6 +294,16 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     v.o_genPtr = bl.put(genPtr); v.o_genSp = bl.put(genSp); v.o_genStoich = bl.put(genStoich);
     v.o_genOrder = bl.put(genOrder);
     v.o_gPtr = bl.put(gPtr); v.o_gEnt = bl.put(gEnt);
+    {
+        std::vector<uint16_t> gCol, tbTCol;
+        for (int k = 0; k < K; k++) {
+            for (int i = gPtr[k]; i < gPtr[k + 1]; i++) gCol.push_back((uint16_t) k);
+            for (int i = tbTPtr[k]; i < tbTPtr[k + 1]; i++) tbTCol.push_back((uint16_t) k);
+        }
+        v.o_gCol = bl.put(gCol);
+        v.o_tbTCol = bl.put(tbTCol);
+    }
+    v.o_gl8Ptr = bl.put(gl8Ptr); v.o_gl8Sp = bl.put(gl8Sp);
     v.o_runs = bl.put(runs);
     v.nRuns = (int32_t) runs.size();
     v.o_view = bl.put(std::vector<unsigned char>(sizeof(MechView), 0)); // patched below

@@ -125,6 +125,11 @@ struct MechView {
     uint32_t o_gPtr;                        // int32[K+1]
     uint32_t o_gEnt;                        // GatherEnt[nGather]
     uint32_t o_gNu;                         // double[nGather] (only read if hasFractional)
+    uint32_t o_gCol;                        // uint16[nGather]: species (list owner) of gather entry i
+    uint32_t o_tbTCol;                      // uint16[nTbEnt]: species of transposed third-body entry i
+    // species of the gather, dealt to 8 lanes with balanced entry counts (longest list first):
+    uint32_t o_gl8Ptr;                      // int32[9]
+    uint32_t o_gl8Sp;                       // uint16[K]
     uint32_t o_runs;                        // RunRec[nRuns]
     int32_t nRuns;
     uint32_t o_view;                        // a copy of this MechView inside the hot region

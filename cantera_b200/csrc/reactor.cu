@@ -139,7 +139,7 @@ void BatchReactorNet::advance(double t)
     // the one-kernel shared-memory integrator (reactor_kernels.cu), which is also the path for
     // mechanisms too large for the thread-per-reactor kernels.
     const char* which = std::getenv("CTB_BDF_KERNEL");
-    const long long cap = batchSlotCap(m_kin->mech());
+    const long long cap = batchSlotCap(m_kin->mech(), m_neq);
     if (cap > 0 && !(which && std::strcmp(which, "persistent") == 0)) {
         long long S = std::min(m_N, cap);
         if (const char* e = std::getenv("CTB_BDF_SLOTS")) S = std::max(1LL, std::min<long long>(m_N, std::atoll(e)));

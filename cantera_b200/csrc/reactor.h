@@ -45,10 +45,10 @@ void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stre
 // ---- batch-synchronous integrator (reactor_batch.cu)
 //! Byte offsets of the slot-interleaved arrays inside the workspace.
 struct BatchLayout {
-    size_t vec, M, perm, sing, ctl, setupList, counters;
+    size_t slots, pc, setupList, counters;
 };
 //! Upper bound of useful slots on this device (0: the mechanism does not fit the thread kernels).
-long long batchSlotCap(const DeviceMech& m);
+long long batchSlotCap(const DeviceMech& m, int neq);
 size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay);
 //! Integrates every reactor of b to b.tout with S slots; synchronous (returns when all reactors are
 //! done). Returns the number of control/rhs/setup rounds.

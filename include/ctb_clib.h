@@ -113,6 +113,11 @@ int32_t ctb_getError(int32_t bufLen, char* buf);
 int32_t ctb_nDevices(void);
 /* "0.1.0 sm_100a" style version string; same length convention as ctb_getError. */
 int32_t ctb_version(int32_t bufLen, char* buf);
+/* Measured FP64 throughput of `device` in TFLOP/s: a register-resident DFMA micro-benchmark
+ * (8 independent chains per thread, every SM full), timed with CUDA events. This is the roofline
+ * denominator of the FP64-bound kernels (MEASURED_PEAKS.json has no FP64 entry).
+ * Returns -999.999 with an error set on failure. */
+double ctb_fp64PeakTflops(int32_t device);
 
 /* ---- BatchedGasKinetics: Kinetics / BulkKinetics for N states ---------------------------- */
 

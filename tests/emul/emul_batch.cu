@@ -70,15 +70,15 @@ int main(int argc, char** argv)
     b.counter = &counter; b.t0 = 0.0; b.tout = th[0]; b.rtol = 1e-9; b.atol = 1e-15 * 0.1; b.atolUser = 0;
     b.maxSteps = 20000; b.restart = 1; b.ignDT = th[1]; b.crateFloor = 0.0;
 
-    std::vector<double> vec((size_t) SLOT_VECS * n * S), M((size_t) n * n * S);
-    std::vector<int> perm(n * S), sing(S, 0), setupList(S);
-    std::vector<BatchCtl> ctl(S);
-    for (auto& c : ctl) { std::memset(&c, 0, sizeof(c)); c.pc = PC_NEW; }
-    int setupCount = 0, nActive = S;
     SlotMem mem = {};
-    mem.vec = vec.data();
-    mem.M = M.data(); mem.perm = perm.data(); mem.sing = sing.data(); mem.ctl = ctl.data();
+    const unsigned long long slotBytes = slotLayout(n, mem);
+    std::vector<double> slotStore((size_t) slotBytes * S / 8 + 32, 0.0);
+    std::vector<int> setupList(S), pcArr(S, PC_NEW);
+    int setupCount = 0, nActive = S;
+    mem.slots = reinterpret_cast<unsigned char*>(slotStore.data());
+    mem.pc = pcArr.data();
     mem.setupCount = &setupCount; mem.setupList = setupList.data(); mem.nActive = &nActive; mem.S = S;
+    for (int s = 0; s < S; s++) mem.ctl(s)->pc = PC_NEW;
 
     const Solo solo;
     std::vector<double> xs(2 * n), yy(n), f0(n), f1(n), J((size_t) n * n);
@@ -86,20 +86,22 @@ int main(int argc, char** argv)
     for (;; rounds++) {
         setupCount = 0;
         for (int s = 0; s < S; s++) {
-            BatchBdf<Solo, 1> bdf(solo, b, mem, s, xs.data());
+            if (pcArr[s] == PC_IDLE) continue;
+            BatchBdf<Solo, 1> bdf(solo, b, mem, s, mem.block(s), xs.data());
             bdf.run();
         }
         if (nActive == 0) break;
         for (int s = 0; s < S; s++) {
-            if (ctl[s].pc == PC_IDLE) continue;
-            double* sv = vec.data() + (size_t) s * SLOT_VECS * n;
-            hostRhs(pm, ctl[s].P, sv + 8 * n, sv + 9 * n);
+            if (pcArr[s] == PC_IDLE) continue;
+            double* sv = mem.vec(s);
+            hostRhs(pm, mem.ctl(s)->P, sv + 8 * n, sv + 9 * n);
         }
         for (int e = 0; e < setupCount; e++) {
             const int s = setupList[e];
-            const double gamma = ctl[s].gamma;
-            for (int i = 0; i < n; i++) yy[i] = vec[((size_t) s * SLOT_VECS + 8) * n + i];
-            hostRhs(pm, ctl[s].P, yy.data(), f0.data());
+            const double gamma = mem.ctl(s)->gamma;
+            const double Ps = mem.ctl(s)->P;
+            for (int i = 0; i < n; i++) yy[i] = mem.vec(s)[8 * n + i];
+            hostRhs(pm, Ps, yy.data(), f0.data());
             double ntot = 0.0;
             for (int i = 1; i < n; i++) ntot += yy[i];
             for (int j = 0; j < n; j++) {
@@ -107,7 +109,7 @@ int main(int argc, char** argv)
                 const double d = (j == 0) ? save * 1.4901161193847656e-08
                                           : std::fmax(std::fabs(save) * 1e-7, 1e-11 * ntot);
                 yy[j] = save + d;
-                hostRhs(pm, ctl[s].P, yy.data(), f1.data());
+                hostRhs(pm, Ps, yy.data(), f1.data());
                 yy[j] = save;
                 for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * (f1[i] - f0[i]) / d;
             }
@@ -128,11 +130,11 @@ int main(int argc, char** argv)
                     for (int i = k + 1; i < n; i++) J[(size_t) j * n + i] -= J[(size_t) k * n + i] * ukj;
                 }
             }
-            sing[s] = fail;
-            for (int i = 0; i < n; i++) perm[(size_t) s * n + i] = id[i];
+            mem.ctl(s)->sing = fail;
+            for (int i = 0; i < n; i++) mem.perm(s)[i] = id[i];
             for (int col = 0; col < n; col++)
                 for (int row = 0; row < n; row++)
-                    M[(size_t) s * n * n + (size_t) col * n + row] = (row == col) ? 1.0 / J[(size_t) col * n + row] : J[(size_t) col * n + row];
+                    mem.M(s)[(size_t) col * n + row] = (row == col) ? 1.0 / J[(size_t) col * n + row] : J[(size_t) col * n + row];
         }
     }
     std::fprintf(stderr, "rounds %lld\n", rounds);
