@@ -27,7 +27,7 @@ def _build(name):
     src = os.path.join(EMUL, name + ".cu")
     deps = [src] + [os.path.join(ROOT, "cantera_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "cantera_b200", "csrc"))]
     if not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
-        subprocess.check_call([NVCC, "-std=c++17", "-O2", "-x", "cu", "-o", exe, src,
+        subprocess.check_call([NVCC, "-std=c++17", "-O2", "-gencode", "arch=compute_100a,code=sm_100a", "-x", "cu", "-o", exe, src,
                                os.path.join(ROOT, "cantera_b200", "csrc", "mech_pack.cpp"),
                                "-diag-suppress", "177", "-Wno-deprecated-gpu-targets"])
     return exe
