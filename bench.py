@@ -24,6 +24,14 @@ GRI = dict(K=53, R=325)
 FLOP_PER_STATE = 38374.0        # algorithmic FP64 flop per gri30 wdot evaluation
 BYTES_PER_STATE = 8 * (53 + 2) + 8 * 53  # 864 B: T, P, Y in; wdot out
 FP64_PEAK_TFLOPS_NOMINAL = 148 * 64 * 2 * 1.965e9 / 1e12  # 37.2: no FP64 entry in MEASURED_PEAKS.json
+WDOT_TRAFFIC_BYTES_PER_STATE = 822.0  # dram read+write per state, ncu --set full (profiles/r01_rates_kernel*.txt)
+# ignition: algorithmic FP64 flop per reactor from the solver's own counters:
+# n_rhs (F_wdot + 6K) + n_setup (2/3 (K+1)^3 + F_jac) + n_newton 2 (K+1)^2, F_jac ~ 1.5 F_wdot
+def ignition_flops(stats, K=53):
+    n = K + 1
+    st = stats.reshape(-1, 8).sum(axis=0).astype(float)
+    rhs, setups, nni = st[1], st[3], st[4]
+    return rhs * (FLOP_PER_STATE + 6 * K) + setups * (2.0 / 3.0 * n ** 3 + 1.5 * FLOP_PER_STATE) + nni * 2.0 * n * n
 
 
 def parse():
@@ -36,6 +44,7 @@ def parse():
     ap.add_argument("--states", type=int, default=1 << 22)
     ap.add_argument("--reactors", type=int, default=1 << 16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ignition", action="store_true", help="wdot workload: skip the short ignition run reported under 'ignition'")
     return ap.parse_args()
 
 
@@ -219,6 +228,13 @@ def ours(args):
         torch.cuda.synchronize()
 
     launches = 0
+    # FP64 roofline denominator: measured live by the library's DFMA micro-benchmark (MEASURED_PEAKS.json
+    # carries no FP64 figure); the nominal number is kept beside it
+    from cantera_b200 import clib
+    fp64_peak = float(clib.lib().ctb_fp64PeakTflops(local))
+    if not fp64_peak > 0:
+        fp64_peak = FP64_PEAK_TFLOPS_NOMINAL
+    ign_stats = {}
     if args.workload == "wdot":
         n = args.states
         T, P, Y = make_states(torch, n, K, 20261104 + rank, dev)
@@ -245,13 +261,14 @@ def ours(args):
             net.set_state(T, P, Y)
             net.advance(1e-3)
             state["out"] = net.get_state(device_like=T)
+            ign_stats["stats"] = net.solver_stats()
 
         def step_e2e():
             net.set_state(Tn, Pn, Yn)
             net.advance(1e-3)
             state["host"] = net.get_state()
 
-        units, h2d, d2h, launches_per_step = n, 8 * n * (K + 2), 8 * n * (K + 1), 3
+        units, h2d, d2h, launches_per_step = n, 8 * n * (K + 2), 8 * n * (K + 1), 0
         l2_note = "reactor state and integrator memory %d MB per step" % (n * 8 * 12 * (K + 1) >> 20)
 
     for _ in range(args.warmup):
@@ -269,6 +286,8 @@ def ours(args):
         b.record()
         per_step.append((a, b))
         launches += launches_per_step
+        if args.workload == "ignition":
+            launches += 3 + 4 * net.last_rounds()  # init, contents + (memset-free) control, rhs, setup, lu per round
     ev1.record()
     barrier()
     sampler.stop_flag = True
@@ -312,14 +331,46 @@ def ours(args):
         tflops = FLOP_PER_STATE * units / (kernel_ms * 1e-3) / 1e12
         gbs = BYTES_PER_STATE * units / (kernel_ms * 1e-3) / 1e9
         line["roofline"] = {
-            "bound": "tensor", "achieved": tflops, "peak": FP64_PEAK_TFLOPS_NOMINAL, "unit": "TFLOP/s",
-            "frac": tflops / FP64_PEAK_TFLOPS_NOMINAL, "traffic": None,
-            "note": "FP64 DFMA pipe (no tensor cores on this path); peak = nominal 148 SM x 64 DFMA/clk x 1.965 GHz "
-                    "(MEASURED_PEAKS.json has no FP64 entry); algorithmic flop/state = 38374",
+            "bound": "tensor", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": tflops / fp64_peak, "traffic": WDOT_TRAFFIC_BYTES_PER_STATE * units,
+            "note": "FP64 DFMA pipe (no tensor cores on this path; the contract's 'tensor' slot carries the compute "
+                    "roofline). peak = measured live by ctb_fp64PeakTflops (register-resident DFMA micro-benchmark; "
+                    "nominal 148 SM x 64 DFMA/clk x 1.965 GHz = %.1f); algorithmic flop/state = 38374 (SURVEY.md 8(d)); "
+                    "traffic = dram bytes/state of the ncu capture in profiles/ x states" % FP64_PEAK_TFLOPS_NOMINAL,
             "hbm": {"achieved_gbs": gbs, "peak_gbs": peaks.get("hbm_gbs"), "frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
                     "bytes_per_state": BYTES_PER_STATE},
             "kernel_ms": kernel_ms,
         }
+    if args.workload == "ignition" and "stats" in ign_stats:
+        import numpy as np
+        st = np.asarray(ign_stats["stats"]).reshape(-1, 8)
+        fl = ignition_flops(st)
+        tflops = fl / (kernel_ms * 1e-3) / 1e12
+        tot = st.sum(axis=0)
+        line["roofline"] = {
+            "bound": "tensor", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
+            "traffic": None,
+            "note": "FP64 DFMA pipe; algorithmic flop from the solver's counters: n_rhs (F_wdot + 6K) + n_setup "
+                    "(2/3 (K+1)^3 + 1.5 F_wdot) + n_newton 2 (K+1)^2; peak measured live by ctb_fp64PeakTflops",
+            "per_reactor": {"steps": tot[0] / n, "rhs": tot[1] / n, "setups": tot[3] / n, "newton_iters": tot[4] / n},
+            "rounds": net.last_rounds(), "kernel_ms": kernel_ms,
+        }
+    if args.workload == "wdot" and not args.no_ignition and world == 1:
+        # the second half of BASELINE.json's metric, on a bounded batch (one timed advance after one warm-up)
+        n_ign = 32768
+        Tn, Pn, Yn = make_ignition_states(torch, n_ign, 20261104, dev)
+        Ti, Pi, Yi = (torch.from_numpy(a).to(dev) for a in (Tn, Pn, Yn))
+        net = BatchReactorNet(kin, n_ign)
+        for rep_i in range(2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            net.set_state(Ti, Pi, Yi)
+            net.advance(1e-3)
+            torch.cuda.synchronize()
+            ign_s = time.perf_counter() - t0
+        line["ignition"] = {"metric": "gri30_1ms_ignition_reactors_per_s", "value": n_ign / ign_s, "unit": "reactors/s",
+                            "reactors": n_ign, "seconds": ign_s, "failed": int((net.status() != 0).sum())}
+        net.close()
     if not args.no_cpu_baseline:
         cores = host_cores()
         nref = 400000 * cores if args.workload == "wdot" else 24 * cores

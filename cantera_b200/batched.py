@@ -271,6 +271,10 @@ class BatchReactorNet:
         clib.check(self._lib.ctb_reactornet_eval(self._h, yd.ctypes.data, yd.size, clib.HOST))
         return yd
 
+    def last_rounds(self):
+        """Kernel rounds of the batch-synchronous integrator in the last advance."""
+        return int(clib.check(self._lib.ctb_reactornet_lastRounds(self._h)))
+
     def status(self):
         s = np.empty(self.n_reactors, dtype=np.int32)
         clib.check(self._lib.ctb_reactornet_status(self._h, s.size, s.ctypes.data))

@@ -322,6 +322,11 @@ int32_t ctb_reactornet_advance(int32_t handle, double t)
     return guard([&] { NetCabinet::at(handle)->advance(t); return 0; });
 }
 
+int32_t ctb_reactornet_lastRounds(int32_t handle)
+{
+    return guard([&] { return (int32_t) NetCabinet::at(handle)->lastRounds(); });
+}
+
 double ctb_reactornet_time(int32_t handle)
 {
     return guarded<double>(CTB_DERR, CTB_DERR, [&] { return NetCabinet::at(handle)->time(); });

@@ -154,6 +154,7 @@ void BatchReactorNet::advance(double t)
         }
         cudaCheck(cudaGetLastError(), "batch advance");
     } else {
+        m_lastRounds = 0;
         launchAdvance(m_kin->mech(), b, st);
         cudaCheck(cudaGetLastError(), "advance launch");
     }

@@ -82,6 +82,7 @@ public:
     void setInitialTime(double t0);         // ReactorNet.cpp:172-177
     void advance(double t);                 // ReactorNet.cpp:351-357
     double time() const { return m_time; }
+    long long lastRounds() const { return m_lastRounds; }
     void getState(double* T, double* Y, long long ldY, int memspace);
     //! ReactorNet::getState (ReactorNet.cpp:688-695): y[n*(K+1) + i] = [T, n_1..n_K] of every reactor
     void getStateVector(double* y, long long bufLen, int memspace);

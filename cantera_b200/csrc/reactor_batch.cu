@@ -90,17 +90,27 @@ __global__ void __launch_bounds__(256) batchControlKernel(const ReactorBatch b, 
     for (int s = blockIdx.x * W + warp; s < mem.S; s += gridDim.x * W) {
         if (mem.pc[s] == PC_IDLE) continue;
         unsigned char* gblk = mem.block(s);
+        const long long t0 = mem.prof ? clock64() : 0;
         if (lane == 0) bulkLoad(buf, gblk, (uint32_t) mem.slotBytes, bar);
         barWait(bar, parity);
         parity ^= 1;
+        const long long t1 = mem.prof ? clock64() : 0;
         {
             BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, buf, nullptr);
             bdf.run();
         }
+        const long long t2 = mem.prof ? clock64() : 0;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) bulkStore(gblk, buf, prefix);
         __syncwarp();
+        if (mem.prof && lane == 0) {
+            const long long t3 = clock64();
+            atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 8), (unsigned long long) (t1 - t0));
+            atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 9), (unsigned long long) (t2 - t1));
+            atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 10), (unsigned long long) (t3 - t2));
+            atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 11), 1ULL);
+        }
     }
 }
 
@@ -333,7 +343,7 @@ bool launchSetupT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
     return true;
 }
 
-void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, cudaEvent_t between = nullptr)
 {
     const MechView& v = m.view;
     const size_t groupBytes = (16 + reactorWorkDoubles(v.K, v.R)) * 8;
@@ -351,6 +361,7 @@ void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
     default: throw std::runtime_error("CTB_SETUP_NT must be 32, 64, 128 or 256");
     }
     if (!ok) throw std::runtime_error("mechanism too large for the shared-memory Newton-matrix kernel");
+    if (between) cudaEventRecord(between, stream);
     // factorisation: one warp per flagged matrix
     const size_t region = (size_t) (mem.slotBytes - mem.oPerm);
     const int warps = (int) std::min<size_t>(8, ((size_t) m.smemOptIn - 1024 - 64) / region);
@@ -407,7 +418,7 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     mem.S = (int) S;
     const bool profile = std::getenv("CTB_PROFILE") != nullptr;
     mem.prof = profile ? reinterpret_cast<long long*>(w + l.counters + 64) : nullptr;
-    if (profile) cudaMemsetAsync(mem.prof, 0, 8 * sizeof(long long), stream);
+    if (profile) cudaMemsetAsync(mem.prof, 0, 16 * sizeof(long long), stream);
 
     // ---- rhs kernel: groups of 8 lanes, as many as shared memory holds
     const int rhsGroupDoubles = (2 * n + 4 * v.K + v.R + 1) & ~1;
@@ -436,23 +447,49 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     long long rounds = 0;
     const long long maxRounds = 64LL * b.maxSteps + 1000;
     int active = 1;
+    // CTB_PROFILE: CUDA events around every kernel of a round, read at the 16-round sync points
+    cudaEvent_t ev[16][5];
+    double kernMs[4] = {0, 0, 0, 0};
+    if (profile) for (auto& r : ev) for (auto& e : r) cudaEventCreate(&e);
     while (rounds < maxRounds) {
+        cudaEvent_t* e5 = profile ? ev[rounds & 15] : nullptr;
         cudaMemsetAsync(mem.setupCount, 0, sizeof(int), stream);
+        if (e5) cudaEventRecord(e5[0], stream);
         ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem);
+        if (e5) cudaEventRecord(e5[1], stream);
         batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
-        launchSetup(m, mem, stream);
+        if (e5) cudaEventRecord(e5[2], stream);
+        launchSetup(m, mem, stream, e5 ? e5[3] : nullptr);
+        if (e5) cudaEventRecord(e5[4], stream);
         rounds++;
         if ((rounds & 15) == 0) {
             cudaError_t e = cudaMemcpyAsync(&active, mem.nActive, sizeof(int), cudaMemcpyDeviceToHost, stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
             if (e != cudaSuccess) throw std::runtime_error(std::string("batch integrator: ") + cudaGetErrorString(e));
+            if (profile) {
+                for (auto& r : ev) {
+                    for (int k = 0; k < 4; k++) {
+                        float ms = 0.f;
+                        cudaEventElapsedTime(&ms, r[k], r[k + 1]);
+                        kernMs[k] += ms;
+                    }
+                }
+            }
             if (active <= 0) break;
         }
     }
+    if (profile) {
+        for (auto& r : ev) for (auto& e : r) cudaEventDestroy(e);
+        std::fprintf(stderr, "[ctb profile] kernel time over %lld rounds: control %.1f ms, rhs %.1f ms, setup %.1f ms, lu %.1f ms\n",
+                     rounds, kernMs[0], kernMs[1], kernMs[2], kernMs[3]);
+    }
     if (active > 0) throw std::runtime_error("batch integrator: round limit reached");
     if (profile) {
-        long long h[8];
+        long long h[16];
         cudaMemcpy(h, mem.prof, sizeof(h), cudaMemcpyDeviceToHost);
+        const double nc = h[11] ? (double) h[11] : 1.0;
+        std::fprintf(stderr, "[ctb profile] control: %lld slot visits; cycles per visit: load %.0f, run %.0f, store %.0f\n",
+                     h[11], h[8] / nc, h[9] / nc, h[10] / nc);
         const double ns = h[7] ? (double) h[7] : 1.0;
         std::fprintf(stderr, "[ctb profile] rounds %lld, setups %lld; cycles per setup: rhs+jacdata %.0f, jacobianCi %.0f, "
                      "dense rows %.0f, T column %.0f, I-gJ %.0f, LU %.0f, writeback %.0f\n", rounds, h[7], h[0] / ns,

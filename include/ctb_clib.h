@@ -220,6 +220,9 @@ int32_t ctb_reactornet_status(int32_t handle, int64_t len, int32_t* status);
  * nonlin_conv_fails, err_test_fails, last_order. */
 #define CTB_NSTATS 8
 int32_t ctb_reactornet_solverStats(int32_t handle, int64_t len, int64_t* stats);
+/* Number of control/rhs/setup kernel rounds the batch-synchronous integrator needed in the last
+ * advance (0 when the persistent one-kernel integrator ran). */
+int32_t ctb_reactornet_lastRounds(int32_t handle);
 /* First time each reactor's temperature crossed T0 + dT (ignition delay as in
  * samples/cxx/openmp_ignition/openmp_ignition.cpp:71); NaN where it has not. Set dT before
  * advancing; dT <= 0 disables the monitor. */
