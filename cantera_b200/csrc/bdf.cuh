@@ -222,7 +222,8 @@ __device__ __forceinline__ void reactorRhs(const G& g, const MechView& v, const 
 template <class G>
 __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v, const unsigned char* sm,
                                                   const unsigned char* gm, const ReactorWork& wk, double P,
-                                                  double gamma, long long* prof = nullptr)
+                                                  double gamma, long long* prof = nullptr,
+                                                  const bool formNewton = true)
 {
     const int K = v.K, n = wk.n, ldm = wk.ldm;
     RhsAux aux;
@@ -275,11 +276,13 @@ __device__ __forceinline__ void buildNewtonMatrix(const G& g, const MechView& v,
     const double rdT = 1.0 / dT;
     for (int i = g.lane(); i < n; i += G::NT) wk.M[i] = (wk.tmp[i] - wk.f[i]) * rdT;
     g.sync();
-    for (int j = 0; j < n; j++) {
-        double* col = wk.M + (size_t) j * ldm;
-        for (int i = g.lane(); i < n; i += G::NT) col[i] = (i == j ? 1.0 : 0.0) - gamma * col[i];
+    if (formNewton) {
+        for (int j = 0; j < n; j++) {
+            double* col = wk.M + (size_t) j * ldm;
+            for (int i = g.lane(); i < n; i += G::NT) col[i] = (i == j ? 1.0 : 0.0) - gamma * col[i];
+        }
+        g.sync();
     }
-    g.sync();
     tick(4);
 }
 
@@ -385,6 +388,8 @@ __device__ __forceinline__ void luSolve(const G& g, const ReactorWork& wk)
 // (SURVEY.md Appendix C).
 #define BDF_QMAX 5
 #define BDF_MSBP 20        // max steps between Newton-matrix setups
+#define BDF_MSBJ 50        // max steps between Jacobian evaluations (cvodes_ls_impl.h CVLS_MSBJ)
+#define BDF_DGMAX_JBAD 0.2 // gamma change below which a failure is blamed on the Jacobian (CVLS_DGMAX)
 #define BDF_DGMAX 0.3      // |gamma/gammap - 1| that forces a setup
 #define BDF_MAXCOR 3       // Newton iterations per attempt
 #define BDF_CRDOWN 0.3

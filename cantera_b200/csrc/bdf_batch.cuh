@@ -43,6 +43,7 @@ struct BatchCtl {
     int pc, status, q, L, qwait, qprime, nst, nstlp, nst0, ncf, nef, nflag, m, pass, jcur, callSetup,
         needSing, forceSetup, hinCount, ignPending;
     int nfe, nsetups, nni, ncfn, netf;
+    int nstlj, njac; // step of the last Jacobian evaluation; Jacobian evaluations
     int sing; // written by the setup kernel: non-zero = singular Newton matrix
     long long r;
     double P, atolS, tn, h, hscale, hprime, eta, etamax, gamma, gammap, gamrat, crate, acnrm, savedTq5, rl1,
@@ -51,9 +52,10 @@ struct BatchCtl {
 };
 
 //! Slot-major integrator memory. Every slot owns ONE contiguous, 128-byte aligned block
-//!     [ BatchCtl | vec: zn[0..5], acor, ewt, y, f (10 n doubles) | perm (n ints) | M (n*n doubles) ]
-//! so that the control kernel can bring a whole slot into shared memory with a single TMA bulk copy
-//! and write the mutable prefix (ctl + vec) back with another. y = state the next right-hand side
+//!     [ BatchCtl | vec: zn[0..5], acor, ewt, y, f (10 n doubles) | perm (n ints) | M (n*n doubles) | J (n*n) ]
+//! so that the control kernel can bring what it needs ([0, oJ)) into shared memory with a single TMA
+//! bulk copy and write the mutable prefix (ctl + vec) back with another. J = d(ydot)/dy saved at
+//! the last Jacobian evaluation (CVODES' savedJ: re-used while only gamma changes). y = state the next right-hand side
 //! is evaluated at, f = right-hand side at y; M = LU factors of I - gamma J, column-major
 //! (col * n + row) with the RECIPROCAL pivots on the diagonal; perm = composed row permutation,
 //! (P b)[i] = b[perm[i]].
@@ -61,10 +63,12 @@ struct BatchCtl {
 struct SlotMem {
     unsigned char* slots;
     unsigned long long slotBytes; // multiple of 128
-    unsigned int oVec, oPerm, oM; // byte offsets inside a slot block (multiples of 16)
+    unsigned int oVec, oPerm, oM, oJ; // byte offsets inside a slot block (multiples of 16)
     int* pc;        // [S] copy of ctl.pc (lets kernels skip idle slots without touching the block)
     int* setupCount;
     int* setupList; // [S] slots that need a new Newton matrix in this round
+    int* jacCount;
+    int* jacList;   // [S] the subset whose Jacobian is re-evaluated (the others re-use the saved one)
     int* nActive;   // slots that are not idle
     long long* prof; // optional cycle counters of the setup kernel phases (CTB_PROFILE), or null
     int S, n;
@@ -73,6 +77,7 @@ struct SlotMem {
     CTB_HD double* vec(int s) const { return reinterpret_cast<double*>(block(s) + oVec); }
     CTB_HD int* perm(int s) const { return reinterpret_cast<int*>(block(s) + oPerm); }
     CTB_HD double* M(int s) const { return reinterpret_cast<double*>(block(s) + oM); }
+    CTB_HD double* J(int s) const { return reinterpret_cast<double*>(block(s) + oJ); }
 };
 
 //! Fills the layout fields of a SlotMem for n equations; returns the bytes per slot.
@@ -83,7 +88,8 @@ inline unsigned long long slotLayout(int n, SlotMem& m)
     m.oVec = (unsigned int) up(sizeof(BatchCtl), 16);
     m.oPerm = m.oVec + (unsigned int) (sizeof(double) * SLOT_VECS * n);
     m.oM = m.oPerm + (unsigned int) up(sizeof(int) * n, 16);
-    m.slotBytes = up(m.oM + sizeof(double) * (unsigned long long) n * n, 128);
+    m.oJ = (unsigned int) up(m.oM + sizeof(double) * (unsigned long long) n * n, 128);
+    m.slotBytes = up(m.oJ + sizeof(double) * (unsigned long long) n * n, 128);
     return m.slotBytes;
 }
 
@@ -105,6 +111,13 @@ CTB_HD int fetchAddInt(int* p, int v)
     return o;
 #endif
 }
+
+// The elements a lane owns (i = lane, lane + NT, ...): for a warp the trip count is the compile-time
+// NPL, so the loop unrolls into predicated bodies without loop branches; the one-lane host group
+// walks all n elements.
+#define CTB_FOR_OWN(i) \
+    _Pragma("unroll") for (int j_ = 0; j_ < (G::NT == 1 ? n : NPL); j_++) \
+        if (const int i = g.lane() + G::NT * j_; i < n)
 
 //! The host stand-in for a cooperative group: one "lane" (tests/emul).
 struct Solo {
@@ -145,12 +158,12 @@ struct BatchBdf {
     CTB_HD double& F(int i) const { return vec[9 * n + i]; }
 
     CTB_HD void setEwt() const {
-        for (int i = g.lane(); i < n; i += G::NT) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
+        CTB_FOR_OWN(i) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
     }
     CTB_HD void predict() {
         c.tn += c.h;
         const int q = c.q;
-        for (int i = g.lane(); i < n; i += G::NT) {
+        CTB_FOR_OWN(i) {
             double z[BDF_QMAX + 1];
 #pragma unroll
             for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
@@ -165,7 +178,7 @@ struct BatchBdf {
     CTB_HD void restore() {
         c.tn = c.savedT;
         const int q = c.q;
-        for (int i = g.lane(); i < n; i += G::NT) {
+        CTB_FOR_OWN(i) {
             double z[BDF_QMAX + 1];
 #pragma unroll
             for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
@@ -180,7 +193,7 @@ struct BatchBdf {
     CTB_HD void rescale() {
         double factor = c.eta;
         for (int j = 1; j <= c.q; j++) {
-            for (int i = g.lane(); i < n; i += G::NT) ZN(j, i) *= factor;
+            CTB_FOR_OWN(i) ZN(j, i) *= factor;
             factor *= c.eta;
         }
         c.h = c.hscale * c.eta;
@@ -188,7 +201,7 @@ struct BatchBdf {
     }
     CTB_HD double wrmsAcor() const {
         double sum = 0.0;
-        for (int i = g.lane(); i < n; i += G::NT) {
+        CTB_FOR_OWN(i) {
             const double t = AC(i) * EW(i);
             sum += t * t;
         }
@@ -292,7 +305,7 @@ struct BatchBdf {
                 }
             }
             const double A1 = (-alpha0 - alpha1) / prod;
-            for (int i = g.lane(); i < n; i += G::NT) {
+            CTB_FOR_OWN(i) {
                 const double zL = A1 * ZN(BDF_QMAX, i);
                 ZN(c.L, i) = zL;
 #pragma unroll
@@ -310,7 +323,7 @@ struct BatchBdf {
                     for (int i = BDF_QMAX; i >= 2; i--) if (i <= j + 2) l[i] = l[i] * xi + l[i - 1];
                 }
             }
-            for (int i = g.lane(); i < n; i += G::NT) {
+            CTB_FOR_OWN(i) {
                 const double zq = ZN(q, i);
 #pragma unroll
                 for (int j = 2; j < BDF_QMAX; j++) if (j < q) ZN(j, i) -= l[j] * zq;
@@ -326,7 +339,7 @@ struct BatchBdf {
         if (q == 1 && c.nst > 1) c.tau[2] = c.tau[1];
         c.tau[1] = c.h;
         const bool saveAcor = (c.qwait - 1 == 1) && (q != BDF_QMAX);
-        for (int i = g.lane(); i < n; i += G::NT) {
+        CTB_FOR_OWN(i) {
             const double a = AC(i);
 #pragma unroll
             for (int j = 0; j <= BDF_QMAX; j++) if (j <= q) ZN(j, i) += c.l[j] * a;
@@ -364,7 +377,7 @@ struct BatchBdf {
         double etaqm1 = 0.0, etaqp1 = 0.0;
         if (q > 1) {
             double sum = 0.0;
-            for (int i = g.lane(); i < n; i += G::NT) {
+            CTB_FOR_OWN(i) {
                 const double t = ZN(q, i) * EW(i);
                 sum += t * t;
             }
@@ -374,7 +387,7 @@ struct BatchBdf {
         if (q != BDF_QMAX && c.savedTq5 != 0.0) {
             const double cquot = (c.tq[5] / c.savedTq5) * pow(c.h / c.tau[2], (double) L);
             double sum = 0.0;
-            for (int i = g.lane(); i < n; i += G::NT) {
+            CTB_FOR_OWN(i) {
                 const double t = (AC(i) - cquot * ZN(BDF_QMAX, i)) * EW(i);
                 sum += t * t;
             }
@@ -397,7 +410,7 @@ struct BatchBdf {
         } else {
             c.eta = etaqp1;
             c.qprime = q + 1;
-            for (int i = g.lane(); i < n; i += G::NT) ZN(BDF_QMAX, i) = AC(i);
+            CTB_FOR_OWN(i) ZN(BDF_QMAX, i) = AC(i);
         }
         setEta();
     }
@@ -456,54 +469,57 @@ struct BatchBdf {
 #pragma unroll
             for (int j = 0; j < NPL; j++) xr[j] = t[j];
         }
-        for (int k0 = 0; k0 < n - 1; k0 += PF) {
-            double col[PF][NPL];
+        // Forward substitution (unit lower factor), k in chunks of 32 so that the register holding
+        // x_k and the rows that still need the i > k mask are known at compile time. Rows beyond n
+        // read the column's zero padding... there is none, so their lanes are masked by rowOk.
+        bool rowOk[NPL];
 #pragma unroll
-            for (int u = 0; u < PF; u++) {
-                const int k = k0 + u;
+        for (int j = 0; j < NPL; j++) rowOk[j] = lane + 32 * j < n;
 #pragma unroll
-                for (int j = 0; j < NPL; j++) {
-                    const int i = lane + 32 * j;
-                    col[u][j] = (k < n - 1 && i > k && i < n) ? M[(size_t) k * n + i] : 0.0;
+        for (int kc = 0; kc < NPL; kc++) {
+            const int kEnd = min(32 * (kc + 1), n - 1);
+            for (int k0 = 32 * kc; k0 < kEnd; k0 += PF) {
+                double col[PF][NPL];
+#pragma unroll
+                for (int u = 0; u < PF; u++) {
+                    const int k = min(k0 + u, kEnd - 1);
+#pragma unroll
+                    for (int j = kc; j < NPL; j++) col[u][j] = rowOk[j] ? M[(size_t) k * n + lane + 32 * j] : 0.0;
                 }
-            }
 #pragma unroll
-            for (int u = 0; u < PF; u++) {
-                const int k = k0 + u;
-                if (k < n - 1) {
-                    double src = xr[0];
+                for (int u = 0; u < PF; u++) {
+                    const int k = k0 + u;
+                    if (k < kEnd) {
+                        const double bk = __shfl_sync(0xffffffffu, xr[kc], k & 31);
+                        if (lane > (k & 31)) xr[kc] -= col[u][kc] * bk;
 #pragma unroll
-                    for (int jj = 1; jj < NPL; jj++) if ((k >> 5) == jj) src = xr[jj];
-                    const double bk = __shfl_sync(0xffffffffu, src, k & 31);
-#pragma unroll
-                    for (int j = 0; j < NPL; j++) xr[j] -= col[u][j] * bk;
+                        for (int j = kc + 1; j < NPL; j++) xr[j] -= col[u][j] * bk;
+                    }
                 }
             }
         }
-        for (int k1 = n - 1; k1 >= 0; k1 -= PF) {
-            double col[PF][NPL], dk[PF];
+        // Back substitution (upper factor, reciprocal pivots on the diagonal), chunks from the top
 #pragma unroll
-            for (int u = 0; u < PF; u++) {
-                const int k = k1 - u;
+        for (int kc = NPL - 1; kc >= 0; kc--) {
+            const int kTop = min(32 * (kc + 1), n) - 1;
+            for (int k1 = kTop; k1 >= 32 * kc; k1 -= PF) {
+                double col[PF][NPL];
 #pragma unroll
-                for (int j = 0; j < NPL; j++) {
-                    const int i = lane + 32 * j;
-                    col[u][j] = (k >= 0 && i < k) ? M[(size_t) k * n + i] : 0.0;
+                for (int u = 0; u < PF; u++) {
+                    const int k = max(k1 - u, 32 * kc);
+#pragma unroll
+                    for (int j = 0; j <= kc; j++) col[u][j] = rowOk[j] ? M[(size_t) k * n + lane + 32 * j] : 0.0;
                 }
-                dk[u] = (k >= 0) ? M[(size_t) k * n + k] : 0.0;
-            }
 #pragma unroll
-            for (int u = 0; u < PF; u++) {
-                const int k = k1 - u;
-                if (k >= 0) {
-                    double src = xr[0];
+                for (int u = 0; u < PF; u++) {
+                    const int k = k1 - u;
+                    if (k >= 32 * kc) {
+                        // the owner lane holds the pivot's reciprocal in its own column element
+                        const double xk = __shfl_sync(0xffffffffu, xr[kc] * col[u][kc], k & 31);
+                        if (lane == (k & 31)) xr[kc] = xk;
+                        else if (lane < (k & 31)) xr[kc] -= col[u][kc] * xk;
 #pragma unroll
-                    for (int jj = 1; jj < NPL; jj++) if ((k >> 5) == jj) src = xr[jj];
-                    const double xk = __shfl_sync(0xffffffffu, src, k & 31) * dk[u];
-#pragma unroll
-                    for (int j = 0; j < NPL; j++) {
-                        const int i = lane + 32 * j;
-                        xr[j] = (i == k) ? xk : xr[j] - col[u][j] * xk;
+                        for (int j = 0; j < kc; j++) xr[j] -= col[u][j] * xk;
                     }
                 }
             }
@@ -517,17 +533,17 @@ struct BatchBdf {
         if (status == CTB_STATUS_OK) {
             // CVodeGetDky, k = 0
             const double sc = (p.tout - c.tn) / c.h;
-            for (int i = g.lane(); i < n; i += G::NT) {
+            CTB_FOR_OWN(i) {
                 double acc = ZN(c.q, i);
                 for (int j = c.q - 1; j >= 0; j--) acc = acc * sc + ZN(j, i);
                 yg[i] = acc;
             }
         } else {
-            for (int i = g.lane(); i < n; i += G::NT) yg[i] = ZN(0, i);
+            CTB_FOR_OWN(i) yg[i] = ZN(0, i);
         }
         double* hist = p.hist + r * p.histStride;
         for (int j = 0; j < 6; j++)
-            for (int i = g.lane(); i < n; i += G::NT) hist[j * n + i] = ZN(j, i);
+            CTB_FOR_OWN(i) hist[j * n + i] = ZN(j, i);
         if (g.lane() != 0) return;
         double* hs = hist + 6 * n;
         hs[0] = c.q; hs[1] = c.qwait; hs[2] = c.qprime; hs[3] = c.nst; hs[4] = c.nstlp;
@@ -539,7 +555,7 @@ struct BatchBdf {
         long long* st = p.stats + r * CTB_NSTATS;
         st[STAT_STEPS] += c.nst - c.nst0;
         st[STAT_RHS] += c.nfe;
-        st[STAT_JAC] += c.nsetups;
+        st[STAT_JAC] += c.njac;
         st[STAT_SETUPS] += c.nsetups;
         st[STAT_NLITERS] += c.nni;
         st[STAT_NCFAILS] += c.ncfn;
@@ -569,14 +585,15 @@ struct BatchBdf {
                 }
                 c.r = r;
                 c.P = p.P[r];
-                c.nfe = c.nsetups = c.nni = c.ncfn = c.netf = 0;
+                c.nfe = c.nsetups = c.nni = c.ncfn = c.netf = c.njac = 0;
+                c.nstlj = 0;
                 c.Tign = p.ignDT > 0.0 ? p.T0[r] + p.ignDT : 0.0;
                 c.ignPending = p.ignDT > 0.0 && !(p.tIgn[r] == p.tIgn[r]);
                 c.needSing = 0;
                 if (p.restart) {
                     const double* yg = p.y + r * n;
                     double moles = 0.0;
-                    for (int i = g.lane(); i < n; i += G::NT) {
+                    CTB_FOR_OWN(i) {
                         const double yi = yg[i];
                         ZN(0, i) = yi;
                         Y(i) = yi;
@@ -604,7 +621,7 @@ struct BatchBdf {
                 }
                 const double* hist = p.hist + r * p.histStride;
                 for (int j = 0; j < 6; j++)
-                    for (int i = g.lane(); i < n; i += G::NT) ZN(j, i) = hist[j * n + i];
+                    CTB_FOR_OWN(i) ZN(j, i) = hist[j * n + i];
                 const double* hs = hist + 6 * n;
                 c.q = (int) hs[0]; c.qwait = (int) hs[1]; c.qprime = (int) hs[2]; c.nst = (int) hs[3];
                 c.nstlp = (int) hs[4];
@@ -622,7 +639,7 @@ struct BatchBdf {
                 st = X_ADVANCE;
             } else if (st == PC_START_F0) {
                 // cvHin (Bdf::initialStep of bdf.cuh), first part
-                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) = F(i);
+                CTB_FOR_OWN(i) ZN(1, i) = F(i);
                 const double tdist = fabs(p.tout - p.t0);
                 const double tround = 2.220446049250313e-16 * fmax(fabs(p.t0), fabs(p.tout));
                 if (tdist < 2.0 * tround) {
@@ -632,7 +649,7 @@ struct BatchBdf {
                 }
                 c.hlb = 100.0 * tround;
                 double hubInv = 0.0;
-                for (int i = g.lane(); i < n; i += G::NT) {
+                CTB_FOR_OWN(i) {
                     const double den = 0.1 * fabs(ZN(0, i)) + 1.0 / EW(i);
                     hubInv = fmax(hubInv, fabs(ZN(1, i)) / den);
                 }
@@ -648,13 +665,13 @@ struct BatchBdf {
                 c.hg = sqrt(c.hlb * hub);
                 c.hnew = c.hg;
                 c.hinCount = 1;
-                for (int i = g.lane(); i < n; i += G::NT) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                CTB_FOR_OWN(i) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
                 c.nfe++;
                 c.pc = PC_HIN;
                 break;
             } else if (st == PC_HIN) {
                 double sum = 0.0;
-                for (int i = g.lane(); i < n; i += G::NT) {
+                CTB_FOR_OWN(i) {
                     const double t = (F(i) - ZN(1, i)) / c.hg * EW(i);
                     sum += t * t;
                 }
@@ -683,7 +700,7 @@ struct BatchBdf {
                 }
                 if (next) {
                     c.hinCount++;
-                    for (int i = g.lane(); i < n; i += G::NT) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
+                    CTB_FOR_OWN(i) Y(i) = c.hg * ZN(1, i) + ZN(0, i);
                     c.nfe++;
                     c.pc = PC_HIN;
                     break;
@@ -700,7 +717,7 @@ struct BatchBdf {
                     continue;
                 }
                 c.h = c.hscale = c.hprime = c.h0;
-                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) *= c.h;
+                CTB_FOR_OWN(i) ZN(1, i) *= c.h;
                 st = X_ADVANCE;
             } else if (st == X_ADVANCE) {
                 if (!(c.tn < p.tout)) {
@@ -742,15 +759,31 @@ struct BatchBdf {
                 c.pass = 0;
                 st = X_NLS_PASS;
             } else if (st == X_NLS_PASS) {
-                for (int i = g.lane(); i < n; i += G::NT) {
+                CTB_FOR_OWN(i) {
                     Y(i) = ZN(0, i);
                     AC(i) = 0.0;
                 }
                 c.m = 0;
                 c.delp = 0.0;
                 if (c.callSetup) {
-                    if (g.lane() == 0) mem.setupList[fetchAddInt(mem.setupCount, 1)] = s;
-                    c.nfe += 2;
+                    // cvLsSetup (ext/sundials/src/cvodes/cvodes_ls.c:1614-1700): the saved Jacobian is
+                    // re-used unless it is older than 50 steps or implicated in a convergence failure
+                    const int convfail = (c.pass == 1) ? 2 : (c.nflag == NFLAG_PREV_CONV_FAIL ? 1 : 0);
+                    const double dgamma = fabs(c.gamrat - 1.0);
+                    // (measured: re-using the Jacobian costs ~28 % more steps on the golden gri30 cases and
+                    // buys nothing net, so the default re-evaluates it at every setup; p.reuseJac selects
+                    // CVODES' behaviour)
+                    const bool jbad = !p.reuseJac || c.nst == 0 || c.nst > c.nstlj + BDF_MSBJ
+                                      || (convfail == 2 && dgamma < BDF_DGMAX_JBAD) || convfail == 1 || c.forceSetup;
+                    if (g.lane() == 0) {
+                        mem.setupList[fetchAddInt(mem.setupCount, 1)] = s;
+                        if (jbad) mem.jacList[fetchAddInt(mem.jacCount, 1)] = s;
+                    }
+                    if (jbad) {
+                        c.nfe += 2;
+                        c.njac++;
+                        c.nstlj = c.nst;
+                    }
                     c.nsetups++;
                     c.callSetup = 0;
                     c.forceSetup = 0;
@@ -758,7 +791,7 @@ struct BatchBdf {
                     c.crate = 1.0;
                     c.gammap = c.gamma;
                     c.nstlp = c.nst;
-                    c.jcur = 1;
+                    c.jcur = jbad ? 1 : 0;
                     c.needSing = 1;
                 } else {
                     c.nfe++;
@@ -889,19 +922,19 @@ struct BatchBdf {
                 c.h *= c.eta;
                 c.hscale = c.h;
                 c.qwait = BDF_LONG_WAIT;
-                for (int i = g.lane(); i < n; i += G::NT) Y(i) = ZN(0, i);
+                CTB_FOR_OWN(i) Y(i) = ZN(0, i);
                 c.nfe++;
                 c.pc = PC_RESTART1;
                 break;
             } else if (st == PC_RESTART1) {
-                for (int i = g.lane(); i < n; i += G::NT) ZN(1, i) = c.h * F(i);
+                CTB_FOR_OWN(i) ZN(1, i) = c.h * F(i);
                 st = X_ATTEMPT;
             } else if (st == X_STEP_OK) {
                 completeStep();
                 prepareNextStep(c.dsm);
                 c.etamax = BDF_ETAMX2;
                 const double t2 = c.tq[2];
-                for (int i = g.lane(); i < n; i += G::NT) AC(i) *= t2;
+                CTB_FOR_OWN(i) AC(i) *= t2;
                 g.sync();
                 const double Tnow = ZN(0, 0);
                 if (!(Tnow == Tnow)) {

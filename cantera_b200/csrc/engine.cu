@@ -64,7 +64,7 @@ BatchedGasKinetics::BatchedGasKinetics(const ctb_mech_tables& tables, int device
     cudaCheck(cudaMemcpy(m_dev.dBlob, m_packed.blob.data(), m_packed.blob.size(), cudaMemcpyHostToDevice),
               "cudaMemcpy(mechanism)");
     cudaCheck(cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking), "cudaStreamCreate");
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSTAGE; i++) {
         cudaCheck(cudaStreamCreateWithFlags(&m_copyStream[i], cudaStreamNonBlocking), "cudaStreamCreate");
         cudaCheck(cudaEventCreateWithFlags(&m_evt[i], cudaEventDisableTiming), "cudaEventCreate");
     }
@@ -74,7 +74,7 @@ BatchedGasKinetics::~BatchedGasKinetics()
 {
     cudaSetDevice(m_dev.device);
     if (m_dev.dBlob) cudaFree(m_dev.dBlob);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSTAGE; i++) {
         if (m_copyStream[i]) cudaStreamDestroy(m_copyStream[i]);
         if (m_evt[i]) cudaEventDestroy(m_evt[i]);
     }
@@ -178,11 +178,11 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
     for (double* p : outsW) nW += p != nullptr;
     for (double* p : outsR) nR += p != nullptr;
     const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) nW * K + (size_t) nR * R);
-    long long chunk = std::max<long long>(1024, std::min<long long>(N, (long long) ((256u << 20) / perState)));
-    chunk = std::min<long long>(chunk, std::max<long long>(1024, (N + 15) / 16));
-    for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
+    long long chunk = std::max<long long>(1024, std::min<long long>(N, (long long) ((128u << 20) / perState)));
+    chunk = std::min<long long>(chunk, std::max<long long>(1024, (N + 31) / 32));
+    for (int b = 0; b < NSTAGE; b++) m_stage[b].reserve((size_t) chunk * perState);
     int b = 0;
-    for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
+    for (long long n0 = 0; n0 < N; n0 += chunk, b = (b + 1) % NSTAGE) {
         const long long n = std::min(chunk, N - n0);
         cudaStream_t st = m_copyStream[b];
         double* d = m_stage[b].as<double>();
@@ -211,8 +211,7 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
             }
         }
     }
-    cudaCheck(cudaStreamSynchronize(m_copyStream[0]), "cudaStreamSynchronize");
-    cudaCheck(cudaStreamSynchronize(m_copyStream[1]), "cudaStreamSynchronize");
+    for (int i = 0; i < NSTAGE; i++) cudaCheck(cudaStreamSynchronize(m_copyStream[i]), "cudaStreamSynchronize");
 }
 
 void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P, const double* Y,
@@ -239,11 +238,11 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
     }
     if (memspace != CTB_HOST) throw CtbError("BatchedGasKinetics::jacobian", "memspace must be CTB_HOST or CTB_DEVICE");
     const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) K * K);
-    long long chunk = std::max<long long>(256, std::min<long long>(N, (long long) ((256u << 20) / perState)));
-    chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 15) / 16));
-    for (int b = 0; b < 2; b++) m_stage[b].reserve((size_t) chunk * perState);
+    long long chunk = std::max<long long>(256, std::min<long long>(N, (long long) ((128u << 20) / perState)));
+    chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 31) / 32));
+    for (int b = 0; b < NSTAGE; b++) m_stage[b].reserve((size_t) chunk * perState);
     int b = 0;
-    for (long long n0 = 0; n0 < N; n0 += chunk, b ^= 1) {
+    for (long long n0 = 0; n0 < N; n0 += chunk, b = (b + 1) % NSTAGE) {
         const long long n = std::min(chunk, N - n0);
         cudaStream_t st = m_copyStream[b];
         double* d = m_stage[b].as<double>();
@@ -260,8 +259,7 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
         cudaCheck(cudaMemcpyAsync(jac + n0 * (long long) K * K, dJ, sizeof(double) * n * K * K,
                                   cudaMemcpyDeviceToHost, st), "D2H jac");
     }
-    cudaCheck(cudaStreamSynchronize(m_copyStream[0]), "cudaStreamSynchronize");
-    cudaCheck(cudaStreamSynchronize(m_copyStream[1]), "cudaStreamSynchronize");
+    for (int i = 0; i < NSTAGE; i++) cudaCheck(cudaStreamSynchronize(m_copyStream[i]), "cudaStreamSynchronize");
 }
 
 } // namespace ctb

@@ -80,13 +80,14 @@ private:
     PackedMech m_packed;
     DeviceMech m_dev;
     cudaStream_t m_stream = nullptr;     // own stream
-    cudaStream_t m_copyStream[2] = {nullptr, nullptr};
-    cudaEvent_t m_evt[2] = {nullptr, nullptr};
+    static constexpr int NSTAGE = 4; // chunks in flight: H2D of one overlaps the kernel and D2H of others
+    cudaStream_t m_copyStream[NSTAGE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t m_evt[NSTAGE] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t m_userStream = nullptr;
     bool m_hasUserStream = false;
     bool m_skip3b = false, m_skipFalloff = false;
     double m_rtolDelta = 1e-8;
-    DevBuf m_stage[2]; // device staging for host-memory calls (double buffered)
+    DevBuf m_stage[NSTAGE]; // device staging for host-memory calls
 };
 
 } // namespace ctb

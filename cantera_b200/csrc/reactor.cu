@@ -126,6 +126,7 @@ void BatchReactorNet::advance(double t)
     b.t0 = m_time; b.tout = t; b.rtol = m_rtol; b.atol = m_atol; b.atolUser = m_atolUser;
     b.maxSteps = m_maxSteps; b.restart = m_restart; b.ignDT = m_ignDT;
     if (const char* e = std::getenv("CTB_BDF_CRATE_FLOOR")) b.crateFloor = std::atof(e);
+    if (const char* e = std::getenv("CTB_BDF_REUSE_JAC")) b.reuseJac = std::atoi(e);
     if (const char* e = std::getenv("CTB_BDF_RTOL_SCALE")) b.rtol *= std::atof(e);
     // Absolute-tolerance safety factor. The ignition delay is governed by how accurately the radical
     // pool is tracked while it grows through the atol level; at the reference's own atol our step

@@ -38,6 +38,7 @@ struct ReactorBatch {
     int restart;           // 1: integrator is (re)initialised from y (ReactorNet::setInitialTime)
     double ignDT;          // <= 0: monitor off
     double crateFloor;     // lower bound of the Newton convergence-rate estimate (see bdf.cuh)
+    int reuseJac;          // batch integrator: 1 = keep the Jacobian across setups like CVODES (cvLsSetup)
 };
 
 void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stream);

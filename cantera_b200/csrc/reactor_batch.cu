@@ -76,8 +76,9 @@ __global__ void __launch_bounds__(256) batchControlKernel(const ReactorBatch b, 
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
-    unsigned char* buf = smem + (size_t) warp * mem.slotBytes;
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * mem.slotBytes) + warp;
+    const uint32_t ctlBytes = mem.oJ; // everything but the saved Jacobian
+    unsigned char* buf = smem + (size_t) warp * ctlBytes;
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * ctlBytes) + warp;
     if (lane == 0) {
         const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
@@ -91,7 +92,7 @@ __global__ void __launch_bounds__(256) batchControlKernel(const ReactorBatch b, 
         if (mem.pc[s] == PC_IDLE) continue;
         unsigned char* gblk = mem.block(s);
         const long long t0 = mem.prof ? clock64() : 0;
-        if (lane == 0) bulkLoad(buf, gblk, (uint32_t) mem.slotBytes, bar);
+        if (lane == 0) bulkLoad(buf, gblk, ctlBytes, bar);
         barWait(bar, parity);
         parity ^= 1;
         const long long t1 = mem.prof ? clock64() : 0;
@@ -170,18 +171,19 @@ __global__ void __launch_bounds__(512) batchSetupKernel(const MechView v, const 
     const G g(base, 1 + gInCta);
     const ReactorWork wk = carveWork(base + 16, v.K, v.R);
     const int n = wk.n, ldm = wk.ldm;
-    const int count = *mem.setupCount;
+    const int count = *mem.jacCount;
     for (int e = blockIdx.x * groups + gInCta; e < count; e += gridDim.x * groups) {
-        const int s = mem.setupList[e];
+        const int s = mem.jacList[e];
         const double P = mem.ctl(s)->P;
         const double gamma = mem.ctl(s)->gamma;
         const double* ys = mem.vec(s) + 8 * n;
         for (int i = g.lane(); i < n; i += NT) wk.y[i] = ys[i];
         g.sync();
-        buildNewtonMatrix(g, v, sm, gmech, wk, P, gamma, mem.prof);
+        buildNewtonMatrix(g, v, sm, gmech, wk, P, gamma, mem.prof, false); // J only: the LU kernel forms I - gamma J
         long long tk = mem.prof ? clock64() : 0;
-        // the unfactored matrix goes to the slot's block (column-major n x n); batchLuKernel factors it
-        double* dstM = mem.M(s);
+        // J = d(ydot)/dy goes to the slot's block (column-major n x n), where it stays until the next
+        // evaluation; batchLuKernel forms and factors I - gamma J from it
+        double* dstM = mem.J(s);
         for (int e2 = g.lane(); e2 < n * n; e2 += NT) {
             const int col = e2 / n, row = e2 - col * n;
             dstM[e2] = wk.M[(size_t) col * ldm + row];
@@ -204,7 +206,7 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
-    const uint32_t region = (uint32_t) (mem.slotBytes - mem.oPerm);
+    const uint32_t region = (uint32_t) (mem.oJ - mem.oPerm); // [perm | M]
     unsigned char* buf = smem + (size_t) warp * region;
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * region) + warp;
     if (lane == 0) {
@@ -216,15 +218,24 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
     const int n = mem.n;
     int* perm = reinterpret_cast<int*>(buf);
     double* M = reinterpret_cast<double*>(buf + (mem.oM - mem.oPerm));
+    double* dummy = reinterpret_cast<double*>(smem + (size_t) W * region + 64) + 32 * warp;
     const int count = *mem.setupCount;
     uint32_t parity = 0;
     long long tk = mem.prof ? clock64() : 0;
     for (int e = blockIdx.x * W + warp; e < count; e += gridDim.x * W) {
         const int s = mem.setupList[e];
         unsigned char* gblk = mem.block(s) + mem.oPerm;
-        if (lane == 0) bulkLoad(buf, gblk, region, bar);
+        if (lane == 0) bulkLoad(M, mem.J(s), ((uint32_t) (n * n) * 8u + 15u) & ~15u, bar);
         barWait(bar, parity);
         parity ^= 1;
+        {
+            const double gamma = mem.ctl(s)->gamma;
+            for (int e2 = lane; e2 < n * n; e2 += 32) {
+                const int col = e2 / n, row = e2 - col * n;
+                M[e2] = (row == col ? 1.0 : 0.0) - gamma * M[e2];
+            }
+            __syncwarp();
+        }
         int fail = 0;
         for (int k = 0; k < n; k++) {
             double* ck = M + (size_t) k * n;
@@ -267,16 +278,27 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
                     ck[i] = l[r];
                 }
             }
+            // rank-1 update, branch-free: lanes without a row in a 32-row chunk update a private
+            // dummy word instead (l = 0 there), the chunk count is warp-uniform
             const int rows = n - k - 1;
-#pragma unroll 2
+            const int chunks = (rows + 31) >> 5;
+            long long off[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int i = k + 1 + lane + 32 * r;
+                off[r] = (i < n) ? (long long) i : (long long) (dummy - M) + lane; // relative to column 0
+            }
+#pragma unroll 4
             for (int j = k + 1; j < n; j++) {
                 double* cj = M + (size_t) j * n;
                 const double akj = cj[k];
-                double* cji = cj + k + 1 + lane;
-                if (lane < rows) cji[0] -= l[0] * akj;
-                if (lane + 32 < rows) cji[32] -= l[1] * akj;
-                if (lane + 64 < rows) cji[64] -= l[2] * akj;
-                if (lane + 96 < rows) cji[96] -= l[3] * akj;
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    if (r < chunks) {
+                        double* t = (off[r] < n) ? cj + off[r] : M + off[r];
+                        *t -= l[r] * akj;
+                    }
+                }
             }
             __syncwarp();
         }
@@ -363,10 +385,10 @@ void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, c
     if (!ok) throw std::runtime_error("mechanism too large for the shared-memory Newton-matrix kernel");
     if (between) cudaEventRecord(between, stream);
     // factorisation: one warp per flagged matrix
-    const size_t region = (size_t) (mem.slotBytes - mem.oPerm);
-    const int warps = (int) std::min<size_t>(8, ((size_t) m.smemOptIn - 1024 - 64) / region);
+    const size_t region = (size_t) (mem.oJ - mem.oPerm);
+    const int warps = (int) std::min<size_t>(8, ((size_t) m.smemOptIn - 1024 - 64) / (region + 256));
     if (warps < 1) throw std::runtime_error("Newton matrix does not fit in shared memory");
-    const size_t luSmem = (size_t) warps * region + 64;
+    const size_t luSmem = (size_t) warps * region + 64 + (size_t) warps * 32 * 8;
     cudaFuncSetAttribute(batchLuKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) luSmem);
     batchLuKernel<<<m.numSMs, warps * 32, luSmem, stream>>>(mem);
 }
@@ -377,7 +399,8 @@ long long batchSlotCap(const DeviceMech& m, int neq)
 {
     SlotMem tmp = {};
     const unsigned long long slotBytes = slotLayout(neq, tmp);
-    if (slotBytes + 64 > (unsigned long long) m.smemOptIn - 1024) return 0; // a slot must fit the control kernel's buffer
+    (void) slotBytes;
+    if (tmp.oJ + 64ull > (unsigned long long) m.smemOptIn - 1024) return 0; // a slot must fit the control kernel's buffer
     if ((neq + 31) / 32 > 4) return 0;
     // enough slots for several waves of every kernel, bounded by ~8 GB of slot memory
     long long cap = (long long) m.numSMs * 512;
@@ -394,7 +417,7 @@ size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay)
     BatchLayout l;
     l.slots = take((size_t) slotBytes * S);
     l.pc = take(sizeof(int) * S);
-    l.setupList = take(sizeof(int) * S);
+    l.setupList = take(sizeof(int) * 2 * S);
     l.counters = take(256);
     if (lay) *lay = l;
     return off;
@@ -413,8 +436,10 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     mem.slots = w + l.slots;
     mem.pc = reinterpret_cast<int*>(w + l.pc);
     mem.setupList = reinterpret_cast<int*>(w + l.setupList);
+    mem.jacList = mem.setupList + S;
     mem.setupCount = reinterpret_cast<int*>(w + l.counters);
     mem.nActive = mem.setupCount + 1;
+    mem.jacCount = mem.setupCount + 2;
     mem.S = (int) S;
     const bool profile = std::getenv("CTB_PROFILE") != nullptr;
     mem.prof = profile ? reinterpret_cast<long long*>(w + l.counters + 64) : nullptr;
@@ -432,9 +457,9 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     const int rhsGrid = (int) std::max<long long>(1, std::min<long long>((S + rhsGroups - 1) / rhsGroups, m.numSMs));
 
     // ---- control kernel: one shared-memory slot buffer per warp
-    int ctlWarps = (int) std::min<size_t>(8, (budget - 64) / mem.slotBytes);
+    int ctlWarps = (int) std::min<size_t>(8, (budget - 64) / mem.oJ);
     if (ctlWarps < 1) throw std::runtime_error("a reactor slot does not fit in shared memory");
-    const size_t ctlSmem = (size_t) ctlWarps * mem.slotBytes + 64;
+    const size_t ctlSmem = (size_t) ctlWarps * mem.oJ + 64;
     const int npl = (n + 31) / 32;
     if (npl > 4) throw std::runtime_error("more than 128 equations per reactor: use the persistent integrator");
     const int ctlGrid = (int) std::max<long long>(1, std::min<long long>((S + ctlWarps - 1) / ctlWarps, m.numSMs));
@@ -454,6 +479,7 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     while (rounds < maxRounds) {
         cudaEvent_t* e5 = profile ? ev[rounds & 15] : nullptr;
         cudaMemsetAsync(mem.setupCount, 0, sizeof(int), stream);
+        cudaMemsetAsync(mem.jacCount, 0, sizeof(int), stream);
         if (e5) cudaEventRecord(e5[0], stream);
         ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem);
         if (e5) cudaEventRecord(e5[1], stream);

@@ -73,11 +73,12 @@ int main(int argc, char** argv)
     SlotMem mem = {};
     const unsigned long long slotBytes = slotLayout(n, mem);
     std::vector<double> slotStore((size_t) slotBytes * S / 8 + 32, 0.0);
-    std::vector<int> setupList(S), pcArr(S, PC_NEW);
-    int setupCount = 0, nActive = S;
+    std::vector<int> setupList(S), jacList(S), pcArr(S, PC_NEW);
+    int setupCount = 0, jacCount = 0, nActive = S;
     mem.slots = reinterpret_cast<unsigned char*>(slotStore.data());
     mem.pc = pcArr.data();
     mem.setupCount = &setupCount; mem.setupList = setupList.data(); mem.nActive = &nActive; mem.S = S;
+    mem.jacCount = &jacCount; mem.jacList = jacList.data();
     for (int s = 0; s < S; s++) mem.ctl(s)->pc = PC_NEW;
 
     const Solo solo;
@@ -85,6 +86,7 @@ int main(int argc, char** argv)
     long long rounds = 0;
     for (;; rounds++) {
         setupCount = 0;
+        jacCount = 0;
         for (int s = 0; s < S; s++) {
             if (pcArr[s] == PC_IDLE) continue;
             BatchBdf<Solo, 1> bdf(solo, b, mem, s, mem.block(s), xs.data());
@@ -96,9 +98,9 @@ int main(int argc, char** argv)
             double* sv = mem.vec(s);
             hostRhs(pm, mem.ctl(s)->P, sv + 8 * n, sv + 9 * n);
         }
-        for (int e = 0; e < setupCount; e++) {
-            const int s = setupList[e];
-            const double gamma = mem.ctl(s)->gamma;
+        // Jacobian evaluations (finite differences here; analytic on the GPU) -> saved J of the slot
+        for (int e = 0; e < jacCount; e++) {
+            const int s = jacList[e];
             const double Ps = mem.ctl(s)->P;
             for (int i = 0; i < n; i++) yy[i] = mem.vec(s)[8 * n + i];
             hostRhs(pm, Ps, yy.data(), f0.data());
@@ -111,8 +113,15 @@ int main(int argc, char** argv)
                 yy[j] = save + d;
                 hostRhs(pm, Ps, yy.data(), f1.data());
                 yy[j] = save;
-                for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * (f1[i] - f0[i]) / d;
+                for (int i = 0; i < n; i++) mem.J(s)[(size_t) j * n + i] = (f1[i] - f0[i]) / d;
             }
+        }
+        // Newton matrices I - gamma J from the saved Jacobians, factored
+        for (int e = 0; e < setupCount; e++) {
+            const int s = setupList[e];
+            const double gamma = mem.ctl(s)->gamma;
+            for (int j = 0; j < n; j++)
+                for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * mem.J(s)[(size_t) j * n + i];
             int fail = 0;
             std::vector<int> id(n);
             for (int i = 0; i < n; i++) id[i] = i;
