@@ -112,12 +112,9 @@ CTB_HD int fetchAddInt(int* p, int v)
 #endif
 }
 
-// The elements a lane owns (i = lane, lane + NT, ...): for a warp the trip count is the compile-time
-// NPL, so the loop unrolls into predicated bodies without loop branches; the one-lane host group
-// walks all n elements.
-#define CTB_FOR_OWN(i) \
-    _Pragma("unroll") for (int j_ = 0; j_ < (G::NT == 1 ? n : NPL); j_++) \
-        if (const int i = g.lane() + G::NT * j_; i < n)
+// The elements a lane owns (i = lane, lane + NT, ...). (A fully unrolled, predicated form measured
+// slower in the control kernel than this plain loop.)
+#define CTB_FOR_OWN(i) for (int i = g.lane(); i < n; i += G::NT)
 
 //! The host stand-in for a cooperative group: one "lane" (tests/emul).
 struct Solo {
@@ -447,11 +444,74 @@ struct BatchBdf {
     //! A warp: element i = lane + 32 j lives in xr[j]. Columns of the factors are streamed from HBM
     //! (consecutive lanes, consecutive addresses) eight at a time ahead of the dependent chain;
     //! the pivot element travels by shuffle.
+    //! Forward substitution steps k in [kBeg, kEnd) of chunk KC (rows 32 KC .. 32 KC + 31 hold x_k):
+    //! eight columns are fetched ahead of the dependent chain, every mask is applied to the fetched
+    //! column element (off the chain), so a step is two shuffles and NPL - KC fused multiply-adds.
+    template <int KC, int BLK>
+    __device__ __forceinline__ void fwdBlock(double (&xr)[NPL], const double* __restrict__ M, int k, int lane,
+                                             bool lastOk) const {
+        double c[BLK][NPL];
+#pragma unroll
+        for (int u = 0; u < BLK; u++) {
+            const double* ck = M + (size_t) (k + u) * n + lane;
+            const int kk = (k + u) & 31;
+#pragma unroll
+            for (int j = KC; j < NPL; j++) {
+                bool ok = true;
+                if (j == KC) ok = lane > kk;              // strictly below the diagonal
+                if (j == NPL - 1) ok = ok && lastOk;      // row < n
+                c[u][j] = ok ? ck[32 * j] : 0.0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < BLK; u++) {
+            const double bk = __shfl_sync(0xffffffffu, xr[KC], (k + u) & 31);
+#pragma unroll
+            for (int j = KC; j < NPL; j++) xr[j] = fma(-c[u][j], bk, xr[j]);
+        }
+    }
+    //! Back substitution steps k, k-1, .., k-BLK+1 of chunk KC (reciprocal pivots on the diagonal).
+    template <int KC, int BLK>
+    __device__ __forceinline__ void bwdBlock(double (&xr)[NPL], const double* __restrict__ M, int k, int lane) const {
+        double c[BLK][NPL], d[BLK];
+#pragma unroll
+        for (int u = 0; u < BLK; u++) {
+            const double* ck = M + (size_t) (k - u) * n;
+            const int kk = (k - u) & 31;
+            d[u] = ck[k - u];
+#pragma unroll
+            for (int j = 0; j <= KC; j++) c[u][j] = (j < KC || lane < kk) ? ck[lane + 32 * j] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < BLK; u++) {
+            const int kk = (k - u) & 31;
+            const double xk = __shfl_sync(0xffffffffu, xr[KC], kk) * d[u];
+#pragma unroll
+            for (int j = 0; j < KC; j++) xr[j] = fma(-c[u][j], xk, xr[j]);
+            xr[KC] = (lane == kk) ? xk : fma(-c[u][KC], xk, xr[KC]);
+        }
+    }
+    template <int KC>
+    __device__ __forceinline__ void fwdChunk(double (&xr)[NPL], const double* __restrict__ M, int lane, bool lastOk) const {
+        const int kEnd = min(32 * (KC + 1), n - 1);
+        int k = 32 * KC;
+        for (; k + 8 <= kEnd; k += 8) fwdBlock<KC, 8>(xr, M, k, lane, lastOk);
+        for (; k < kEnd; k++) fwdBlock<KC, 1>(xr, M, k, lane, lastOk);
+    }
+    template <int KC>
+    __device__ __forceinline__ void bwdChunk(double (&xr)[NPL], const double* __restrict__ M, int lane) const {
+        int k = min(32 * (KC + 1), n) - 1;
+        for (; k - 7 >= 32 * KC; k -= 8) bwdBlock<KC, 8>(xr, M, k, lane);
+        for (; k >= 32 * KC; k--) bwdBlock<KC, 1>(xr, M, k, lane);
+    }
+
+    //! A warp: element i = lane + 32 j lives in xr[j]. x <- (LU)^-1 P x with the factors in shared
+    //! memory (luSolve of bdf.cuh; reciprocal pivots, composed permutation); the pivot element of
+    //! every step travels by shuffle.
     __device__ __forceinline__ void solveWarp(double (&xr)[NPL]) const {
         const double* __restrict__ M = MPtr;
         const int* __restrict__ perm = permPtr;
         const int lane = g.lane();
-        constexpr int PF = 8;
         {
             double t[NPL];
 #pragma unroll
@@ -469,61 +529,15 @@ struct BatchBdf {
 #pragma unroll
             for (int j = 0; j < NPL; j++) xr[j] = t[j];
         }
-        // Forward substitution (unit lower factor), k in chunks of 32 so that the register holding
-        // x_k and the rows that still need the i > k mask are known at compile time. Rows beyond n
-        // read the column's zero padding... there is none, so their lanes are masked by rowOk.
-        bool rowOk[NPL];
-#pragma unroll
-        for (int j = 0; j < NPL; j++) rowOk[j] = lane + 32 * j < n;
-#pragma unroll
-        for (int kc = 0; kc < NPL; kc++) {
-            const int kEnd = min(32 * (kc + 1), n - 1);
-            for (int k0 = 32 * kc; k0 < kEnd; k0 += PF) {
-                double col[PF][NPL];
-#pragma unroll
-                for (int u = 0; u < PF; u++) {
-                    const int k = min(k0 + u, kEnd - 1);
-#pragma unroll
-                    for (int j = kc; j < NPL; j++) col[u][j] = rowOk[j] ? M[(size_t) k * n + lane + 32 * j] : 0.0;
-                }
-#pragma unroll
-                for (int u = 0; u < PF; u++) {
-                    const int k = k0 + u;
-                    if (k < kEnd) {
-                        const double bk = __shfl_sync(0xffffffffu, xr[kc], k & 31);
-                        if (lane > (k & 31)) xr[kc] -= col[u][kc] * bk;
-#pragma unroll
-                        for (int j = kc + 1; j < NPL; j++) xr[j] -= col[u][j] * bk;
-                    }
-                }
-            }
-        }
-        // Back substitution (upper factor, reciprocal pivots on the diagonal), chunks from the top
-#pragma unroll
-        for (int kc = NPL - 1; kc >= 0; kc--) {
-            const int kTop = min(32 * (kc + 1), n) - 1;
-            for (int k1 = kTop; k1 >= 32 * kc; k1 -= PF) {
-                double col[PF][NPL];
-#pragma unroll
-                for (int u = 0; u < PF; u++) {
-                    const int k = max(k1 - u, 32 * kc);
-#pragma unroll
-                    for (int j = 0; j <= kc; j++) col[u][j] = rowOk[j] ? M[(size_t) k * n + lane + 32 * j] : 0.0;
-                }
-#pragma unroll
-                for (int u = 0; u < PF; u++) {
-                    const int k = k1 - u;
-                    if (k >= 32 * kc) {
-                        // the owner lane holds the pivot's reciprocal in its own column element
-                        const double xk = __shfl_sync(0xffffffffu, xr[kc] * col[u][kc], k & 31);
-                        if (lane == (k & 31)) xr[kc] = xk;
-                        else if (lane < (k & 31)) xr[kc] -= col[u][kc] * xk;
-#pragma unroll
-                        for (int j = 0; j < kc; j++) xr[j] -= col[u][j] * xk;
-                    }
-                }
-            }
-        }
+        const bool lastOk = lane + 32 * (NPL - 1) < n;
+        fwdChunk<0>(xr, M, lane, lastOk);
+        if (NPL > 1) fwdChunk<(NPL > 1 ? 1 : 0)>(xr, M, lane, lastOk);
+        if (NPL > 2) fwdChunk<(NPL > 2 ? 2 : 0)>(xr, M, lane, lastOk);
+        if (NPL > 3) fwdChunk<(NPL > 3 ? 3 : 0)>(xr, M, lane, lastOk);
+        if (NPL > 3) bwdChunk<(NPL > 3 ? 3 : 0)>(xr, M, lane);
+        if (NPL > 2) bwdChunk<(NPL > 2 ? 2 : 0)>(xr, M, lane);
+        if (NPL > 1) bwdChunk<(NPL > 1 ? 1 : 0)>(xr, M, lane);
+        bwdChunk<0>(xr, M, lane);
     }
 #endif
 

@@ -218,7 +218,6 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
     const int n = mem.n;
     int* perm = reinterpret_cast<int*>(buf);
     double* M = reinterpret_cast<double*>(buf + (mem.oM - mem.oPerm));
-    double* dummy = reinterpret_cast<double*>(smem + (size_t) W * region + 64) + 32 * warp;
     const int count = *mem.setupCount;
     uint32_t parity = 0;
     long long tk = mem.prof ? clock64() : 0;
@@ -230,9 +229,9 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
         parity ^= 1;
         {
             const double gamma = mem.ctl(s)->gamma;
-            for (int e2 = lane; e2 < n * n; e2 += 32) {
-                const int col = e2 / n, row = e2 - col * n;
-                M[e2] = (row == col ? 1.0 : 0.0) - gamma * M[e2];
+            for (int col = 0; col < n; col++) {
+                double* cc = M + (size_t) col * n;
+                for (int row = lane; row < n; row += 32) cc[row] = (row == col ? 1.0 : 0.0) - gamma * cc[row];
             }
             __syncwarp();
         }
@@ -278,27 +277,17 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
                     ck[i] = l[r];
                 }
             }
-            // rank-1 update, branch-free: lanes without a row in a 32-row chunk update a private
-            // dummy word instead (l = 0 there), the chunk count is warp-uniform
+            // rank-1 update: lanes own rows (at most 4 chunks of 32 for n <= 128)
             const int rows = n - k - 1;
-            const int chunks = (rows + 31) >> 5;
-            long long off[4];
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const int i = k + 1 + lane + 32 * r;
-                off[r] = (i < n) ? (long long) i : (long long) (dummy - M) + lane; // relative to column 0
-            }
-#pragma unroll 4
+#pragma unroll 2
             for (int j = k + 1; j < n; j++) {
                 double* cj = M + (size_t) j * n;
                 const double akj = cj[k];
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    if (r < chunks) {
-                        double* t = (off[r] < n) ? cj + off[r] : M + off[r];
-                        *t -= l[r] * akj;
-                    }
-                }
+                double* cji = cj + k + 1 + lane;
+                if (lane < rows) cji[0] -= l[0] * akj;
+                if (lane + 32 < rows) cji[32] -= l[1] * akj;
+                if (lane + 64 < rows) cji[64] -= l[2] * akj;
+                if (lane + 96 < rows) cji[96] -= l[3] * akj;
             }
             __syncwarp();
         }
