@@ -9,7 +9,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libctb.so")
-SOURCES = ["mech_pack.cpp", "kin_kernels.cu", "engine.cu", "reactor.cu", "reactor_kernels.cu", "reactor_batch.cu", "ctb_clib.cu"]
+# (source, extra nvcc flags, object name); reactor_advance.cu is compiled once per group width
+SOURCES = [(s, [], s + ".o") for s in ("mech_pack.cpp", "kin_kernels.cu", "engine.cu", "reactor.cu",
+                                       "reactor_kernels.cu", "reactor_batch.cu", "ctb_clib.cu")]
+SOURCES += [("reactor_advance.cu", ["-DCTB_ADV_NT=%d" % nt], "reactor_advance_%d.o" % nt) for nt in (128, 256, 64, 32)]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--fmad=true",
               "-diag-suppress", "177"]
@@ -45,12 +48,13 @@ def build(force=False, verbose=False):
     nvcc = _nvcc()
     hdr_time = max(os.path.getmtime(p) for p in _deps() if p.endswith((".h", ".cuh")))
 
-    def compile_one(src):
+    def compile_one(item):
+        src, extra, oname = item
         s = os.path.join(CSRC, src)
-        o = os.path.join(OBJ, src + ".o")
+        o = os.path.join(OBJ, oname)
         if not force and os.path.exists(o) and os.path.getmtime(o) > max(os.path.getmtime(s), hdr_time):
             return o
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", s, "-o", o]
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + extra + ["-x", "cu", "-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
@@ -58,7 +62,7 @@ def build(force=False, verbose=False):
             sys.stderr.write(r.stderr)
         return o
 
-    with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
+    with ThreadPoolExecutor(max_workers=min(os.cpu_count() or 4, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-cudart", "static"]
     r = subprocess.run(cmd, capture_output=True, text=True)

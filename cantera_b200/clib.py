@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libctb.so")
+# CTB_LIB: an alternative build of the same library (kernel experiments); the default is in-tree
+LIB_PATH = os.environ.get("CTB_LIB") or os.path.join(_HERE, "libctb.so")
 _LIB = None
 
 ERR = -999

@@ -5,6 +5,10 @@
 //   jacKernel<G>           netProductionRates_ddX / _ddCi, dense column-major K x K per state.
 //
 // Shared memory: [hot mechanism tables (TMA bulk copy)] [mbarrier] [per-group work areas].
+// The kinetics kernels keep the library exp(): expHot (rates.cuh) shortens the dependent chain,
+// which pays in the latency-bound reactor kernels (RHS kernel -13 %) but not here, where 13 warps
+// per SM already cover it and the extra clamp costs issue slots (151 vs 153 M states/s measured).
+#define CTB_EXP_LIB
 #include "kin_kernels.h"
 #include "rates_thread.cuh"
 
