@@ -24,7 +24,7 @@ GRI = dict(K=53, R=325)
 FLOP_PER_STATE = 38374.0        # algorithmic FP64 flop per gri30 wdot evaluation
 BYTES_PER_STATE = 8 * (53 + 2) + 8 * 53  # 864 B: T, P, Y in; wdot out
 FP64_PEAK_TFLOPS_NOMINAL = 148 * 64 * 2 * 1.965e9 / 1e12  # 37.2: no FP64 entry in MEASURED_PEAKS.json
-WDOT_TRAFFIC_BYTES_PER_STATE = 871.7  # dram read+write per state, ncu --set full (profiles/r01_rates_kernel*.txt)
+WDOT_TRAFFIC_BYTES_PER_STATE = 874.8  # dram read+write per state, ncu --set full (profiles/r01_rates_kernel*.txt)
 # ignition: algorithmic FP64 flop per reactor from the solver's own counters:
 # n_rhs (F_wdot + 6K) + n_setup (2/3 (K+1)^3 + F_jac) + n_newton 2 (K+1)^2, F_jac ~ 1.5 F_wdot
 def ignition_flops(stats, K=53):
@@ -357,7 +357,7 @@ def ours(args):
         }
     if args.workload == "wdot" and not args.no_ignition and world == 1:
         # the second half of BASELINE.json's metric, on a bounded batch (one timed advance after one warm-up)
-        n_ign = 32768
+        n_ign = 131072
         Tn, Pn, Yn = make_ignition_states(torch, n_ign, 20261104, dev)
         Ti, Pi, Yi = (torch.from_numpy(a).to(dev) for a in (Tn, Pn, Yn))
         net = BatchReactorNet(kin, n_ign)
