@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="wdot", choices=["wdot", "ignition"])
     ap.add_argument("--states", type=int, default=1 << 22)
-    ap.add_argument("--reactors", type=int, default=1 << 16)
+    ap.add_argument("--reactors", type=int, default=1 << 17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ignition", action="store_true", help="wdot workload: skip the short ignition run reported under 'ignition'")
     return ap.parse_args()
