@@ -192,6 +192,7 @@ class BatchReactorNet:
         self.kinetics = kinetics
         self.n_reactors = int(n_reactors)
         self._h = clib.check(self._lib.ctb_reactornet_new(kinetics.handle, self.n_reactors))
+        self._rtol, self._atol = 1e-9, 1e-15  # ReactorNet.h:483-485
 
     def close(self):
         if getattr(self, "_h", None) is not None:
@@ -227,6 +228,13 @@ class BatchReactorNet:
     def atol(self, v):
         clib.check(self._lib.ctb_reactornet_setAbsoluteTolerance(self._h, float(v)))
         self._atol = float(v)
+
+    def effective_tolerances(self):
+        """(rtol, atol of the T row, atol of the species rows, user_set) as the integrator applies them
+        (ctb_reactornet_getTolerances); without a user-set atol the species value is per kmol of contents."""
+        out = np.empty(4)
+        clib.check(self._lib.ctb_reactornet_getTolerances(self._h, 4, out.ctypes.data))
+        return float(out[0]), float(out[1]), float(out[2]), bool(out[3])
 
     def set_max_steps(self, n):
         clib.check(self._lib.ctb_reactornet_setMaxSteps(self._h, int(n)))

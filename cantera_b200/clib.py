@@ -54,6 +54,7 @@ SIGNATURES = {
     "ctb_reactornet_setRelativeTolerance": (_i32, [_i32, _f64]),
     "ctb_reactornet_setAbsoluteTolerance": (_i32, [_i32, _f64]),
     "ctb_reactornet_setMaxSteps": (_i32, [_i32, _i32]),
+    "ctb_reactornet_getTolerances": (_i32, [_i32, _i32, _dp]),
     "ctb_reactornet_setInitialTime": (_i32, [_i32, _f64]),
     "ctb_reactornet_advance": (_i32, [_i32, _f64]),
     "ctb_reactornet_time": (_f64, [_i32]),

@@ -1,24 +1,33 @@
 // bdf_batch.cuh — the BDF/Newton controller of BatchReactorNet as a RESUMABLE per-reactor state
 // machine, for the batch-synchronous integrator of reactor_batch.cu.
 //
-// The persistent kernel of reactor_kernels.cu keeps one reactor's whole integrator (Newton matrix
-// included) in shared memory, which bounds an SM to 3-5 reactors in flight. Here the integrator is
-// cut at the points where it needs the chemistry — a right-hand side, or a new Newton matrix — and
-// everything between two such points is ONE invocation of BatchBdf::run() by ONE WARP:
+// The integrator is cut at the points where it needs the chemistry — a right-hand side, or a new
+// Newton matrix — and everything between two such points is ONE invocation of BatchBdf::run() by
+// ONE WARP:
 //
-//     control (warp/slot)  ->  rhs (thread/slot, rates_thread.cuh)  ->  setup (group/flagged slot)
-//            ^------------------------------------------------------------------------|
+//     control (warp/slot)  ->  rhs (8 lanes/slot)  ->  jacobian (group/flagged slot)  ->  invert
+//            ^----------------------------------------------------------------------------|
 //
 // so that the expensive part (rates) runs as a throughput kernel over all slots at once, and the
-// per-slot data (Nordsieck array, LU factors: ~30 KB for gri30) lives in HBM, one contiguous block
-// per slot: the lanes of the controlling warp read it with consecutive addresses, and the
-// triangular solves stream the factors column by column (prefetched eight columns ahead).
+// per-slot data (Nordsieck array, Newton matrix: ~28 KB for gri30) lives in HBM, one contiguous
+// block per slot. The Newton systems are solved with the EXPLICIT INVERSE of I - gamma J (computed
+// once per setup by a register-resident Gauss-Jordan kernel): a solve is then a matrix-vector
+// product whose matrix is streamed from HBM/L2 with coalesced loads and used exactly once, with no
+// dependent chain — the triangular solves of the first version (two shuffles per pivot, 108 pivots)
+// were two thirds of a controller visit.
 // A slot that finishes its reactor pulls the next one from a global queue (reactors differ ~10x in
 // step count), so all slots stay busy until the queue is empty.
 //
-// The algorithm is the one of bdf.cuh (same constants, same operation order per reactor: the
-// variable-order variable-step fixed-leading-coefficient BDF of VODE/CVODE with CVODES' controller
-// constants, ext/sundials/src/cvodes/cvodes_impl.h:53-126); only its control flow is inverted.
+// PROVENANCE. The step-size / order controller (setCoefficients, adjustOrder, prepareNextStep, the
+// initial-step iteration, the error-test and convergence-failure handling) is a port of the scalar
+// controller arithmetic of SUNDIALS CVODES, ext/sundials/src/cvodes/cvodes.c (cvSetBDF, cvSetTqBDF,
+// cvIncreaseBDF, cvDecreaseBDF, cvHin, cvUpperBoundH0, cvPrepareNextStep, cvComputeEtaqm1/p1,
+// cvChooseEta, cvNlsNewton's convergence test), re-expressed as a resumable state machine so that
+// step counts are comparable with ReactorNet::advance. SUNDIALS is
+//   Copyright (c) 2002-2025, Lawrence Livermore National Security and Southern Methodist University.
+//   All rights reserved. SPDX-License-Identifier: BSD-3-Clause (see ext/sundials/LICENSE).
+// What is original here: the state-machine inversion, the slot layout, the lane-cyclic vector
+// arithmetic, the explicit-inverse Newton solve and the analytic Newton matrix.
 // The arithmetic is __host__ __device__: tests/emul runs it on the CPU.
 #pragma once
 
@@ -43,8 +52,8 @@ struct BatchCtl {
     int pc, status, q, L, qwait, qprime, nst, nstlp, nst0, ncf, nef, nflag, m, pass, jcur, callSetup,
         needSing, forceSetup, hinCount, ignPending;
     int nfe, nsetups, nni, ncfn, netf;
-    int nstlj, njac; // step of the last Jacobian evaluation; Jacobian evaluations
-    int sing; // written by the setup kernel: non-zero = singular Newton matrix
+    int njac; // Jacobian evaluations (one per setup)
+    int sing; // written by the invert kernel: non-zero = singular Newton matrix
     long long r;
     double P, atolS, tn, h, hscale, hprime, eta, etamax, gamma, gammap, gamrat, crate, acnrm, savedTq5, rl1,
         delp, savedT, dsm, hg, hnew, hub, hlb, h0, tPrev, TPrev, Tign;
@@ -52,32 +61,27 @@ struct BatchCtl {
 };
 
 //! Slot-major integrator memory. Every slot owns ONE contiguous, 128-byte aligned block
-//!     [ BatchCtl | vec: zn[0..5], acor, ewt, y, f (10 n doubles) | perm (n ints) | M (n*n doubles) | J (n*n) ]
-//! so that the control kernel can bring what it needs ([0, oJ)) into shared memory with a single TMA
-//! bulk copy and write the mutable prefix (ctl + vec) back with another. J = d(ydot)/dy saved at
-//! the last Jacobian evaluation (CVODES' savedJ: re-used while only gamma changes). y = state the next right-hand side
-//! is evaluated at, f = right-hand side at y; M = LU factors of I - gamma J, column-major
-//! (col * n + row) with the RECIPROCAL pivots on the diagonal; perm = composed row permutation,
-//! (P b)[i] = b[perm[i]].
+//!     [ BatchCtl | vec: zn[0..5], acor, ewt, y, f (10 n doubles) | M (n*n doubles) ]
+//! so that the control kernel can bring its working set ([0, oM): controller + vectors) into shared
+//! memory with a single TMA bulk copy and write it back with another. y = state the next right-hand
+//! side is evaluated at, f = right-hand side at y. M, column-major (col * n + row): the jacobian
+//! kernel leaves J = d(ydot)/dy there, the invert kernel replaces it in place by (I - gamma J)^-1.
 #define SLOT_VECS 10
 struct SlotMem {
     unsigned char* slots;
     unsigned long long slotBytes; // multiple of 128
-    unsigned int oVec, oPerm, oM, oJ; // byte offsets inside a slot block (multiples of 16)
+    unsigned int oVec, oM;  // byte offsets inside a slot block (multiples of 16)
     int* pc;        // [S] copy of ctl.pc (lets kernels skip idle slots without touching the block)
-    int* setupCount;
+    int* setupCount; // [2]: the control kernel of round r appends to [r & 1] and clears [(r + 1) & 1]
     int* setupList; // [S] slots that need a new Newton matrix in this round
-    int* jacCount;
-    int* jacList;   // [S] the subset whose Jacobian is re-evaluated (the others re-use the saved one)
     int* nActive;   // slots that are not idle
     long long* prof; // optional cycle counters of the setup kernel phases (CTB_PROFILE), or null
     int S, n;
+    int parity;     // round & 1
     CTB_HD unsigned char* block(int s) const { return slots + (size_t) s * slotBytes; }
     CTB_HD BatchCtl* ctl(int s) const { return reinterpret_cast<BatchCtl*>(block(s)); }
     CTB_HD double* vec(int s) const { return reinterpret_cast<double*>(block(s) + oVec); }
-    CTB_HD int* perm(int s) const { return reinterpret_cast<int*>(block(s) + oPerm); }
     CTB_HD double* M(int s) const { return reinterpret_cast<double*>(block(s) + oM); }
-    CTB_HD double* J(int s) const { return reinterpret_cast<double*>(block(s) + oJ); }
 };
 
 //! Fills the layout fields of a SlotMem for n equations; returns the bytes per slot.
@@ -86,10 +90,8 @@ inline unsigned long long slotLayout(int n, SlotMem& m)
     auto up = [](unsigned long long x, unsigned long long a) { return (x + a - 1) / a * a; };
     m.n = n;
     m.oVec = (unsigned int) up(sizeof(BatchCtl), 16);
-    m.oPerm = m.oVec + (unsigned int) (sizeof(double) * SLOT_VECS * n);
-    m.oM = m.oPerm + (unsigned int) up(sizeof(int) * n, 16);
-    m.oJ = (unsigned int) up(m.oM + sizeof(double) * (unsigned long long) n * n, 128);
-    m.slotBytes = up(m.oJ + sizeof(double) * (unsigned long long) n * n, 128);
+    m.oM = (unsigned int) up(m.oVec + sizeof(double) * SLOT_VECS * n, 128);
+    m.slotBytes = up(m.oM + sizeof(double) * (unsigned long long) n * n, 128);
     return m.slotBytes;
 }
 
@@ -135,18 +137,25 @@ struct BatchBdf {
     const ReactorBatch& p;
     const SlotMem& mem;
     const int n, s;
-    BatchCtl* const ctlPtr;  // this slot's block: in HBM, or its shared-memory copy
-    double* const vec;
-    const int* const permPtr;
-    const double* const MPtr;
-    double* const xs;  // 2 n doubles of scratch (only used by the one-lane solve)
-    BatchCtl c;
+    BatchCtl* const ctlPtr;  // this slot's controller memory: in HBM, or its shared-memory copy
+    double* const vec;       // the slot's vectors, likewise
+    const double* const MPtr; // (I - gamma J)^-1 of the slot, column-major, in HBM
+    double* const xs;  // n doubles of scratch (only used by the one-lane solve)
+#ifdef CTB_CTL_IN_SMEM
+    BatchCtl& c;       // controller memory is used where it lies (shared memory): fewer registers
+#else
+    BatchCtl c;        // controller memory in registers for the duration of run()
+#endif
 
-    //! blk: the slot's block (SlotMem layout) wherever it currently lives
-    CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, unsigned char* blk, double* xs_)
+    //! blk: the slot's [ctl | vec] prefix wherever it currently lives; Minv: the slot's matrix
+    CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, unsigned char* blk,
+                    const double* Minv, double* xs_)
         : g(g_), p(p_), mem(m_), n(p_.neq), s(s_), ctlPtr(reinterpret_cast<BatchCtl*>(blk)),
-          vec(reinterpret_cast<double*>(blk + m_.oVec)), permPtr(reinterpret_cast<const int*>(blk + m_.oPerm)),
-          MPtr(reinterpret_cast<const double*>(blk + m_.oM)), xs(xs_) {}
+          vec(reinterpret_cast<double*>(blk + m_.oVec)), MPtr(Minv), xs(xs_)
+#ifdef CTB_CTL_IN_SMEM
+          , c(*reinterpret_cast<BatchCtl*>(blk))
+#endif
+    {}
 
     CTB_HD double& ZN(int j, int i) const { return vec[j * n + i]; }
     CTB_HD double& AC(int i) const { return vec[6 * n + i]; }
@@ -419,125 +428,61 @@ struct BatchBdf {
         return v;
     }
 
-    //! One lane: xs[0..n) <- (LU)^-1 P xs (xs has 2 n doubles). The factors carry the reciprocal
-    //! pivots on the diagonal and the composed permutation (luSolve of bdf.cuh otherwise).
+    //! One lane (host emulation): xs[0..n) <- Minv * F.
     CTB_HD void solveSerial() const {
         const double* M = MPtr;
-        const int* perm = permPtr;
-        double* t = xs + n;
-        for (int i = 0; i < n; i++) t[i] = xs[perm[i]];
-        for (int k = 0; k < n - 1; k++) {
-            const double bk = t[k];
-            const double* ck = M + (size_t) k * n;
-            for (int i = k + 1; i < n; i++) t[i] -= ck[i] * bk;
+        for (int i = 0; i < n; i++) xs[i] = 0.0;
+        for (int j = 0; j < n; j++) {
+            const double bj = F(j);
+            const double* cj = M + (size_t) j * n;
+            for (int i = 0; i < n; i++) xs[i] += cj[i] * bj;
         }
-        for (int k = n - 1; k >= 0; k--) {
-            const double* ck = M + (size_t) k * n;
-            const double xk = t[k] * ck[k];
-            t[k] = xk;
-            for (int i = 0; i < k; i++) t[i] -= ck[i] * xk;
-        }
-        for (int i = 0; i < n; i++) xs[i] = t[i];
     }
 
 #ifdef __CUDA_ARCH__
-    //! A warp: element i = lane + 32 j lives in xr[j]. Columns of the factors are streamed from HBM
-    //! (consecutive lanes, consecutive addresses) eight at a time ahead of the dependent chain;
-    //! the pivot element travels by shuffle.
-    //! Forward substitution steps k in [kBeg, kEnd) of chunk KC (rows 32 KC .. 32 KC + 31 hold x_k):
-    //! eight columns are fetched ahead of the dependent chain, every mask is applied to the fetched
-    //! column element (off the chain), so a step is two shuffles and NPL - KC fused multiply-adds.
-    template <int KC, int BLK>
-    __device__ __forceinline__ void fwdBlock(double (&xr)[NPL], const double* __restrict__ M, int k, int lane,
-                                             bool lastOk) const {
-        double c[BLK][NPL];
+    //! A warp: x = Minv * F with row i = lane + 32 j of x in xr[j]. The right-hand side F is read
+    //! from shared memory (broadcast), the matrix is streamed from global memory column by column
+    //! (consecutive lanes, consecutive addresses; every element is used exactly once, so the loads
+    //! bypass L1 allocation), eight columns in flight per lane and two accumulators per row.
+    __device__ __forceinline__ void gemvWarp(double (&xr)[NPL]) const {
+        const int lane = g.lane();
+        const double* __restrict__ Mg = MPtr + lane;
+        const double* __restrict__ b = vec + 9 * n;
+        const bool lastOk = lane + 32 * (NPL - 1) < n;
+        double a0[NPL], a1[NPL];
 #pragma unroll
-        for (int u = 0; u < BLK; u++) {
-            const double* ck = M + (size_t) (k + u) * n + lane;
-            const int kk = (k + u) & 31;
+        for (int j = 0; j < NPL; j++) { a0[j] = 0.0; a1[j] = 0.0; }
+        int col = 0;
+#pragma unroll 1
+        for (; col + 8 <= n; col += 8) {
+            double m[8][NPL];
 #pragma unroll
-            for (int j = KC; j < NPL; j++) {
-                bool ok = true;
-                if (j == KC) ok = lane > kk;              // strictly below the diagonal
-                if (j == NPL - 1) ok = ok && lastOk;      // row < n
-                c[u][j] = ok ? ck[32 * j] : 0.0;
+            for (int u = 0; u < 8; u++) {
+                const double* ck = Mg + (size_t) (col + u) * n;
+#pragma unroll
+                for (int j = 0; j < NPL; j++) m[u][j] = (j < NPL - 1 || lastOk) ? __ldcs(ck + 32 * j) : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) {
+                const double b0 = b[col + u], b1 = b[col + u + 1];
+#pragma unroll
+                for (int j = 0; j < NPL; j++) {
+                    a0[j] = fma(m[u][j], b0, a0[j]);
+                    a1[j] = fma(m[u + 1][j], b1, a1[j]);
+                }
             }
         }
-#pragma unroll
-        for (int u = 0; u < BLK; u++) {
-            const double bk = __shfl_sync(0xffffffffu, xr[KC], (k + u) & 31);
-#pragma unroll
-            for (int j = KC; j < NPL; j++) xr[j] = fma(-c[u][j], bk, xr[j]);
-        }
-    }
-    //! Back substitution steps k, k-1, .., k-BLK+1 of chunk KC (reciprocal pivots on the diagonal).
-    template <int KC, int BLK>
-    __device__ __forceinline__ void bwdBlock(double (&xr)[NPL], const double* __restrict__ M, int k, int lane) const {
-        double c[BLK][NPL], d[BLK];
-#pragma unroll
-        for (int u = 0; u < BLK; u++) {
-            const double* ck = M + (size_t) (k - u) * n;
-            const int kk = (k - u) & 31;
-            d[u] = ck[k - u];
-#pragma unroll
-            for (int j = 0; j <= KC; j++) c[u][j] = (j < KC || lane < kk) ? ck[lane + 32 * j] : 0.0;
-        }
-#pragma unroll
-        for (int u = 0; u < BLK; u++) {
-            const int kk = (k - u) & 31;
-            const double xk = __shfl_sync(0xffffffffu, xr[KC], kk) * d[u];
-#pragma unroll
-            for (int j = 0; j < KC; j++) xr[j] = fma(-c[u][j], xk, xr[j]);
-            xr[KC] = (lane == kk) ? xk : fma(-c[u][KC], xk, xr[KC]);
-        }
-    }
-    template <int KC>
-    __device__ __forceinline__ void fwdChunk(double (&xr)[NPL], const double* __restrict__ M, int lane, bool lastOk) const {
-        const int kEnd = min(32 * (KC + 1), n - 1);
-        int k = 32 * KC;
-        for (; k + 8 <= kEnd; k += 8) fwdBlock<KC, 8>(xr, M, k, lane, lastOk);
-        for (; k < kEnd; k++) fwdBlock<KC, 1>(xr, M, k, lane, lastOk);
-    }
-    template <int KC>
-    __device__ __forceinline__ void bwdChunk(double (&xr)[NPL], const double* __restrict__ M, int lane) const {
-        int k = min(32 * (KC + 1), n) - 1;
-        for (; k - 7 >= 32 * KC; k -= 8) bwdBlock<KC, 8>(xr, M, k, lane);
-        for (; k >= 32 * KC; k--) bwdBlock<KC, 1>(xr, M, k, lane);
-    }
-
-    //! A warp: element i = lane + 32 j lives in xr[j]. x <- (LU)^-1 P x with the factors in shared
-    //! memory (luSolve of bdf.cuh; reciprocal pivots, composed permutation); the pivot element of
-    //! every step travels by shuffle.
-    __device__ __forceinline__ void solveWarp(double (&xr)[NPL]) const {
-        const double* __restrict__ M = MPtr;
-        const int* __restrict__ perm = permPtr;
-        const int lane = g.lane();
-        {
-            double t[NPL];
+        for (; col < n; col++) {
+            const double* ck = Mg + (size_t) col * n;
+            const double bc = b[col];
 #pragma unroll
             for (int j = 0; j < NPL; j++) {
-                const int i = lane + 32 * j;
-                const int pi = (i < n) ? perm[i] : 0;
-                double val = 0.0;
-#pragma unroll
-                for (int jj = 0; jj < NPL; jj++) {
-                    const double v = __shfl_sync(0xffffffffu, xr[jj], pi & 31);
-                    if ((pi >> 5) == jj) val = v;
-                }
-                t[j] = (i < n) ? val : 0.0;
+                const double mv = (j < NPL - 1 || lastOk) ? __ldcs(ck + 32 * j) : 0.0;
+                a0[j] = fma(mv, bc, a0[j]);
             }
-#pragma unroll
-            for (int j = 0; j < NPL; j++) xr[j] = t[j];
         }
-        const bool lastOk = lane + 32 * (NPL - 1) < n;
-        fwdChunk<0>(xr, M, lane, lastOk);
-        if (NPL > 1) fwdChunk<(NPL > 1 ? 1 : 0)>(xr, M, lane, lastOk);
-        if (NPL > 2) fwdChunk<(NPL > 2 ? 2 : 0)>(xr, M, lane, lastOk);
-        if (NPL > 3) fwdChunk<(NPL > 3 ? 3 : 0)>(xr, M, lane, lastOk);
-        if (NPL > 3) bwdChunk<(NPL > 3 ? 3 : 0)>(xr, M, lane);
-        if (NPL > 2) bwdChunk<(NPL > 2 ? 2 : 0)>(xr, M, lane);
-        if (NPL > 1) bwdChunk<(NPL > 1 ? 1 : 0)>(xr, M, lane);
-        bwdChunk<0>(xr, M, lane);
+#pragma unroll
+        for (int j = 0; j < NPL; j++) xr[j] = a0[j] + a1[j];
     }
 #endif
 
@@ -579,7 +524,9 @@ struct BatchBdf {
 
     //! Returns when the slot waits for a right-hand side (c.pc >= PC_START_F0) or is idle.
     CTB_HD void run() {
+#ifndef CTB_CTL_IN_SMEM
         c = *ctlPtr;
+#endif
         if (c.pc == PC_IDLE) return;
         int st = c.pc;
         int finishStatus = CTB_STATUS_OK;
@@ -600,7 +547,6 @@ struct BatchBdf {
                 c.r = r;
                 c.P = p.P[r];
                 c.nfe = c.nsetups = c.nni = c.ncfn = c.netf = c.njac = 0;
-                c.nstlj = 0;
                 c.Tign = p.ignDT > 0.0 ? p.T0[r] + p.ignDT : 0.0;
                 c.ignPending = p.ignDT > 0.0 && !(p.tIgn[r] == p.tIgn[r]);
                 c.needSing = 0;
@@ -780,24 +726,13 @@ struct BatchBdf {
                 c.m = 0;
                 c.delp = 0.0;
                 if (c.callSetup) {
-                    // cvLsSetup (ext/sundials/src/cvodes/cvodes_ls.c:1614-1700): the saved Jacobian is
-                    // re-used unless it is older than 50 steps or implicated in a convergence failure
-                    const int convfail = (c.pass == 1) ? 2 : (c.nflag == NFLAG_PREV_CONV_FAIL ? 1 : 0);
-                    const double dgamma = fabs(c.gamrat - 1.0);
-                    // (measured: re-using the Jacobian costs ~28 % more steps on the golden gri30 cases and
-                    // buys nothing net, so the default re-evaluates it at every setup; p.reuseJac selects
-                    // CVODES' behaviour)
-                    const bool jbad = !p.reuseJac || c.nst == 0 || c.nst > c.nstlj + BDF_MSBJ
-                                      || (convfail == 2 && dgamma < BDF_DGMAX_JBAD) || convfail == 1 || c.forceSetup;
-                    if (g.lane() == 0) {
-                        mem.setupList[fetchAddInt(mem.setupCount, 1)] = s;
-                        if (jbad) mem.jacList[fetchAddInt(mem.jacCount, 1)] = s;
-                    }
-                    if (jbad) {
-                        c.nfe += 2;
-                        c.njac++;
-                        c.nstlj = c.nst;
-                    }
+                    // cvLsSetup (ext/sundials/src/cvodes/cvodes_ls.c:1614-1700) with the Jacobian
+                    // re-evaluated at every setup: re-using a saved Jacobian like CVODES was measured
+                    // (round 1: ~28 % more steps on the golden gri30 cases, 8.4 k instead of 10.4 k
+                    // reactors/s) and dropped. The jacobian kernel evaluates f(y) and f(y + dT e_T).
+                    if (g.lane() == 0) mem.setupList[fetchAddInt(mem.setupCount + mem.parity, 1)] = s;
+                    c.nfe += 2;
+                    c.njac++;
                     c.nsetups++;
                     c.callSetup = 0;
                     c.forceSetup = 0;
@@ -805,7 +740,7 @@ struct BatchBdf {
                     c.crate = 1.0;
                     c.gammap = c.gamma;
                     c.nstlp = c.nst;
-                    c.jcur = jbad ? 1 : 0;
+                    c.jcur = 1;
                     c.needSing = 1;
                 } else {
                     c.nfe++;
@@ -826,13 +761,12 @@ struct BatchBdf {
                 double sum = 0.0;
 #ifdef __CUDA_ARCH__
                 if (G::NT > 1) {
+                    // residual b = gamma f - (rl1 zn1 + acor) overwrites f (its only use), then
+                    // x = (I - gamma J)^-1 b as a matrix-vector product
+                    CTB_FOR_OWN(i) F(i) = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
+                    g.sync();
                     double xr[NPL];
-#pragma unroll
-                    for (int j = 0; j < NPL; j++) {
-                        const int i = g.lane() + G::NT * j;
-                        xr[j] = (i < n) ? c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i)) : 0.0;
-                    }
-                    solveWarp(xr);
+                    gemvWarp(xr);
 #pragma unroll
                     for (int j = 0; j < NPL; j++) {
                         const int i = g.lane() + G::NT * j;
@@ -848,7 +782,7 @@ struct BatchBdf {
                 } else
 #endif
                 {
-                    for (int i = 0; i < n; i++) xs[i] = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
+                    for (int i = 0; i < n; i++) F(i) = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
                     solveSerial();
                     for (int i = 0; i < n; i++) {
                         const double d = xs[i] * sc;
@@ -969,10 +903,14 @@ struct BatchBdf {
                 st = PC_NEW;
             }
         }
+#ifdef CTB_CTL_IN_SMEM
+        if (g.lane() == 0) mem.pc[s] = c.pc;
+#else
         if (g.lane() == 0) {
             *ctlPtr = c;
             mem.pc[s] = c.pc;
         }
+#endif
     }
 };
 

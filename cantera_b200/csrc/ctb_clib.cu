@@ -312,6 +312,15 @@ int32_t ctb_reactornet_setMaxSteps(int32_t handle, int32_t maxSteps)
     return guard([&] { NetCabinet::at(handle)->setMaxSteps(maxSteps); return 0; });
 }
 
+int32_t ctb_reactornet_getTolerances(int32_t handle, int32_t len, double* out)
+{
+    return guard([&] {
+        if (len < 4 || !out) throw CtbError("ctb_reactornet_getTolerances", "array size (" + std::to_string(len) + ") is too small; needs 4");
+        NetCabinet::at(handle)->getTolerances(out);
+        return 0;
+    });
+}
+
 int32_t ctb_reactornet_setInitialTime(int32_t handle, double t0)
 {
     return guard([&] { NetCabinet::at(handle)->setInitialTime(t0); return 0; });

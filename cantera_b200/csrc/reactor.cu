@@ -89,6 +89,30 @@ void BatchReactorNet::setAbsoluteTolerance(double atol)
     m_restart = true;
 }
 
+// Tolerance mapping. A user-set absolute tolerance is applied exactly as given, to every component
+// (ReactorNet.cpp:200-209, 233-245). The DEFAULT (1e-15, scaled by the reactor's total moles for the
+// species rows: MoleReactor.cpp:64-76) is tightened by kDefaultAtolSafety: this solver converges its
+// Newton iterations with an analytic Jacobian and never cuts a step for a convergence failure, so at
+// equal tolerances it takes ~25 % fewer, larger steps than CVODES does through Cantera, and the
+// radical pool of a long induction period (components far below rtol |y|, controlled by atol alone)
+// is tracked less tightly than the reference happens to track it. The factor restores the
+// reference's accuracy level on the ignition delay; tests/test_gpu_reactor.py checks it on reactors
+// it was not chosen on, and ctb_reactornet_getTolerances reports what is actually applied.
+static constexpr double kDefaultAtolSafety = 0.1;
+
+double BatchReactorNet::effectiveAtol() const
+{
+    return m_atolUser ? m_atol : m_atol * kDefaultAtolSafety;
+}
+
+void BatchReactorNet::getTolerances(double* out4) const
+{
+    out4[0] = m_rtol;
+    out4[1] = effectiveAtol();              // temperature row
+    out4[2] = effectiveAtol();              // species rows; times the reactor's total moles if out4[3] == 0
+    out4[3] = m_atolUser ? 1.0 : 0.0;
+}
+
 void BatchReactorNet::setMaxSteps(int n)
 {
     if (n < 1) throw CtbError("BatchReactorNet::setMaxSteps", "the number of steps must be positive");
@@ -124,26 +148,13 @@ void BatchReactorNet::advance(double t)
     b.tIgn = m_tIgn.as<double>(); b.status = m_status.as<int32_t>(); b.stats = m_stats.as<long long>();
     b.counter = m_counter.as<unsigned long long>();
     b.t0 = m_time; b.tout = t; b.rtol = m_rtol; b.atol = m_atol; b.atolUser = m_atolUser;
-    b.maxSteps = m_maxSteps; b.restart = m_restart; b.ignDT = m_ignDT;
-    if (const char* e = std::getenv("CTB_BDF_CRATE_FLOOR")) b.crateFloor = std::atof(e);
-    if (const char* e = std::getenv("CTB_BDF_REUSE_JAC")) b.reuseJac = std::atoi(e);
-    if (const char* e = std::getenv("CTB_BDF_RTOL_SCALE")) b.rtol *= std::atof(e);
-    // Absolute-tolerance safety factor. The ignition delay is governed by how accurately the radical
-    // pool is tracked while it grows through the atol level; at the reference's own atol our step
-    // sequence (fewer, larger steps than CVODES) leaves a 2e-5 delay shift on nDodecane. A factor 0.1
-    // (+10 % steps) brings delay and end states to within the reference's own integration error
-    // (tools/accuracy_sweep.py, profiles/r01_accuracy_sweep.txt).
-    double atolScale = 0.1;
-    if (const char* e = std::getenv("CTB_BDF_ATOL_SCALE")) atolScale = std::atof(e);
-    b.atol *= atolScale;
-    // Default: the batch-synchronous integrator (reactor_batch.cu). CTB_BDF_KERNEL=persistent selects
-    // the one-kernel shared-memory integrator (reactor_kernels.cu), which is also the path for
-    // mechanisms too large for the thread-per-reactor kernels.
-    const char* which = std::getenv("CTB_BDF_KERNEL");
+    b.maxSteps = m_maxSteps; b.restart = m_restart; b.ignDT = m_ignDT; b.crateFloor = 0.0;
+    b.atol = effectiveAtol();
+    // The batch-synchronous integrator (reactor_batch.cu) handles up to 128 equations per reactor;
+    // larger mechanisms take the one-kernel shared-memory integrator (reactor_kernels.cu).
     const long long cap = batchSlotCap(m_kin->mech(), m_neq);
-    if (cap > 0 && !(which && std::strcmp(which, "persistent") == 0)) {
-        long long S = std::min(m_N, cap);
-        if (const char* e = std::getenv("CTB_BDF_SLOTS")) S = std::max(1LL, std::min<long long>(m_N, std::atoll(e)));
+    if (cap > 0) {
+        const long long S = std::min(m_N, cap);
         if (S != m_slots) {
             m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr));
             m_slots = S;

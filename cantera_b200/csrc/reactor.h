@@ -38,7 +38,6 @@ struct ReactorBatch {
     int restart;           // 1: integrator is (re)initialised from y (ReactorNet::setInitialTime)
     double ignDT;          // <= 0: monitor off
     double crateFloor;     // lower bound of the Newton convergence-rate estimate (see bdf.cuh)
-    int reuseJac;          // batch integrator: 1 = keep the Jacobian across setups like CVODES (cvLsSetup)
 };
 
 void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stream);
@@ -80,6 +79,9 @@ public:
     void setRelativeTolerance(double rtol); // ReactorNet.cpp:190-198
     void setAbsoluteTolerance(double atol); // ReactorNet.cpp:200-209
     void setMaxSteps(int n);                // Integrator::setMaxSteps (CVodesIntegrator.h:131)
+    //! {rtol, atol of the T row, atol of the species rows, 1 if atol was set by the user (else the
+    //! species value is per kmol of reactor contents)} as the integrator applies them
+    void getTolerances(double* out4) const;
     void setInitialTime(double t0);         // ReactorNet.cpp:172-177
     void advance(double t);                 // ReactorNet.cpp:351-357
     double time() const { return m_time; }
@@ -95,6 +97,7 @@ public:
     void ignitionDelay(long long len, double* out);
 
 private:
+    double effectiveAtol() const;
     std::shared_ptr<BatchedGasKinetics> m_kin;
     long long m_N;
     int m_neq;

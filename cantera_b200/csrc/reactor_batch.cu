@@ -1,22 +1,27 @@
 // reactor_batch.cu — the batch-synchronous integrator of BatchReactorNet (SURVEY.md §8 rows
-// a12-a14): rounds of three kernels over a pool of SLOTS,
+// a12-a14): rounds of four kernels over a pool of SLOTS,
 //
-//   batchControlKernel  one warp per slot: the resumable BDF/Newton controller of bdf_batch.cuh
-//                       (triangular solves stream the slot's LU factors from HBM, coalesced)
-//   batchRhsKernel      one thread per slot: reactor right-hand side at the requested state
-//                       (reactor_thread.cuh; species arrays in shared memory, [species][thread])
-//   batchSetupKernel    one cooperative group per FLAGGED slot: analytic Newton matrix + dense LU
-//                       in shared memory (bdf.cuh), factors written back to the slot's block
+//   batchControlKernel  one warp per slot: the resumable BDF/Newton controller of bdf_batch.cuh;
+//                       [controller | vectors] of the slot come in and go out by TMA bulk copies,
+//                       the Newton solve is a matrix-vector product with the slot's explicit
+//                       inverse streamed from HBM/L2 (coalesced, every element used once)
+//   batchRhsKernel      a sub-warp group of 8 lanes per slot: reactor right-hand side at the
+//                       requested state (reactorRhs of bdf.cuh on the rates device code)
+//   batchJacKernel      one cooperative group per FLAGGED slot: analytic J = d(ydot)/dy assembled in
+//                       shared memory, written to the slot's matrix region
+//   batchInvertKernel   one CTA per FLAGGED slot: (I - gamma J)^-1 by Gauss-Jordan elimination with
+//                       partial pivoting, every thread holding (a segment of) one matrix ROW IN
+//                       REGISTERS; only the pivot column and the pivot row travel through shared memory
 //
-// with the per-slot integrator memory in HBM. Compared with the persistent one-kernel integrator
-// of reactor_kernels.cu (3-5 reactors per SM, everything in shared memory) this keeps thousands of
-// reactors in flight per SM-round and runs the chemistry at the throughput of the rates kernels.
+// with the per-slot integrator memory in HBM. Tens of thousands of reactors are in flight per
+// round, so the chemistry runs at the throughput of the rates kernels.
 #include "bdf_batch.cuh"
 
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
+#include <string>
 
 namespace ctb {
 
@@ -30,7 +35,31 @@ __global__ void batchInitKernel(SlotMem mem)
         mem.ctl(s)->sing = 0;
         mem.pc[s] = PC_NEW;
     }
-    if (s == 0) *mem.nActive = mem.S;
+    if (s == 0) {
+        *mem.nActive = mem.S;
+        mem.setupCount[0] = 0;
+        mem.setupCount[1] = 0;
+    }
+}
+
+//! After an abnormal end of the round loop (safety net; every reactor is already bounded by
+//! maxSteps): reactors still in a slot or in the queue get CTB_STATUS_TOO_MANY_STEPS and keep their
+//! last accepted state, so that a numerical failure never fails the call.
+__global__ void batchAbortKernel(ReactorBatch b, SlotMem mem)
+{
+    const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < mem.S && mem.pc[i] != PC_IDLE) {
+        const BatchCtl* c = mem.ctl((int) i);
+        if (mem.pc[i] != PC_NEW) {
+            const long long r = c->r;
+            const double* zn0 = mem.vec((int) i);
+            for (int k = 0; k < b.neq; k++) b.y[r * b.neq + k] = zn0[k];
+            b.status[r] = CTB_STATUS_TOO_MANY_STEPS;
+        }
+    }
+    const long long head = (long long) *b.counter;
+    const long long r = head + i;
+    if (r < b.N) b.status[r] = CTB_STATUS_TOO_MANY_STEPS;
 }
 
 // ---- warp-level TMA helpers (1-D bulk copies, one mbarrier per warp)
@@ -65,39 +94,53 @@ __device__ __forceinline__ void bulkStore(void* dstGlobal, const void* srcSmem, 
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
+__device__ __forceinline__ void prefetchL2(const void* srcGlobal, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(srcGlobal), "r"(bytes) : "memory");
+}
 
-//! Persistent CTAs, one warp per slot at a time. The warp brings the slot's whole block (controller
-//! memory, Nordsieck array, LU factors: 28 KB for gri30) into its own shared-memory buffer with ONE
-//! TMA bulk copy, runs the controller there (BatchBdf::run: no global-memory latency inside the
-//! step logic or the triangular solves), and writes the mutable prefix back with a bulk store.
-//! The other warps of the CTA cover the copy latency; 8 buffers per SM keep HBM busy.
+#ifndef CTB_CTL_WARPS
+#define CTB_CTL_WARPS 16
+#endif
+
+//! Persistent CTAs, one warp per slot at a time. The warp brings the slot's [controller | vectors]
+//! prefix (4.8 KB for gri30) into its own shared-memory buffer with ONE TMA bulk copy, asks the L2
+//! for the slot's Newton-matrix inverse at the same time (bulk prefetch), runs the controller
+//! (BatchBdf::run: vector arithmetic on shared memory, the Newton solve as a streamed matrix-vector
+//! product) and writes the prefix back with a bulk store. The other warps of the CTA cover the
+//! latencies; the matrix never occupies shared memory, so 16 warps per SM are resident.
 template <int NPL>
-__global__ void __launch_bounds__(256) batchControlKernel(const ReactorBatch b, const SlotMem mem)
+__global__ void __launch_bounds__(CTB_CTL_WARPS * 32, 1) batchControlKernel(const ReactorBatch b, const SlotMem mem)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
-    const uint32_t ctlBytes = mem.oJ; // everything but the saved Jacobian
-    unsigned char* buf = smem + (size_t) warp * ctlBytes;
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * ctlBytes) + warp;
+    const uint32_t prefix = mem.oM; // ctl + vec
+    unsigned char* buf = smem + (size_t) warp * prefix;
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * prefix) + warp;
     if (lane == 0) {
         const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) mem.setupCount[mem.parity ^ 1] = 0; // next round's list
     __syncwarp();
     const SubWarp<32> g;
     uint32_t parity = 0;
-    const uint32_t prefix = mem.oPerm; // ctl + vec
+    const uint32_t matBytes = ((uint32_t) (mem.n * mem.n) * 8u + 15u) & ~15u;
     for (int s = blockIdx.x * W + warp; s < mem.S; s += gridDim.x * W) {
-        if (mem.pc[s] == PC_IDLE) continue;
+        const int pc = mem.pc[s];
+        if (pc == PC_IDLE) continue;
         unsigned char* gblk = mem.block(s);
         const long long t0 = mem.prof ? clock64() : 0;
-        if (lane == 0) bulkLoad(buf, gblk, ctlBytes, bar);
+        if (lane == 0) {
+            bulkLoad(buf, gblk, prefix, bar);
+            if (pc == PC_NEWTON) prefetchL2(gblk + mem.oM, matBytes);
+        }
         barWait(bar, parity);
         parity ^= 1;
         const long long t1 = mem.prof ? clock64() : 0;
         {
-            BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, buf, nullptr);
+            BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, buf, mem.M(s), nullptr);
             bdf.run();
         }
         const long long t2 = mem.prof ? clock64() : 0;
@@ -116,7 +159,7 @@ __global__ void __launch_bounds__(256) batchControlKernel(const ReactorBatch b, 
 }
 
 //! Reactor right-hand side at the requested state of every active slot: a sub-warp group of 8
-//! lanes per slot (reactorRhs of bdf.cuh on rates.cuh), work areas in shared memory.
+//! lanes per slot (reactorRhs of bdf.cuh on the rates device code), work areas in shared memory.
 __global__ void __launch_bounds__(512) batchRhsKernel(const MechView v, const unsigned char* __restrict__ gmech,
                                                       const SlotMem mem, const int groupDoubles)
 {
@@ -154,11 +197,12 @@ __global__ void __launch_bounds__(512) batchRhsKernel(const MechView v, const un
     }
 }
 
-//! Newton matrix I - gamma J at the slot's requested state and its LU factors, for the slots the
-//! controller flagged in this round. One NamedGroup of NT threads per slot.
+//! J = d(ydot)/dy at the slot's requested state, for the slots the controller flagged in this round.
+//! One NamedGroup of NT threads per slot; J goes to the slot's matrix region (column-major n x n),
+//! where batchInvertKernel turns it into (I - gamma J)^-1.
 template <int NT>
-__global__ void __launch_bounds__(512) batchSetupKernel(const MechView v, const unsigned char* __restrict__ gmech,
-                                                        const SlotMem mem, const int groupDoubles)
+__global__ void __launch_bounds__(512) batchJacKernel(const MechView v, const unsigned char* __restrict__ gmech,
+                                                      const SlotMem mem, const int groupDoubles)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + v.hotBytes);
@@ -171,19 +215,17 @@ __global__ void __launch_bounds__(512) batchSetupKernel(const MechView v, const 
     const G g(base, 1 + gInCta);
     const ReactorWork wk = carveWork(base + 16, v.K, v.R);
     const int n = wk.n, ldm = wk.ldm;
-    const int count = *mem.jacCount;
+    const int count = mem.setupCount[mem.parity];
     for (int e = blockIdx.x * groups + gInCta; e < count; e += gridDim.x * groups) {
-        const int s = mem.jacList[e];
+        const int s = mem.setupList[e];
         const double P = mem.ctl(s)->P;
         const double gamma = mem.ctl(s)->gamma;
         const double* ys = mem.vec(s) + 8 * n;
         for (int i = g.lane(); i < n; i += NT) wk.y[i] = ys[i];
         g.sync();
-        buildNewtonMatrix(g, v, sm, gmech, wk, P, gamma, mem.prof, false); // J only: the LU kernel forms I - gamma J
+        buildNewtonMatrix(g, v, sm, gmech, wk, P, gamma, mem.prof, false); // J only
         long long tk = mem.prof ? clock64() : 0;
-        // J = d(ydot)/dy goes to the slot's block (column-major n x n), where it stays until the next
-        // evaluation; batchLuKernel forms and factors I - gamma J from it
-        double* dstM = mem.J(s);
+        double* dstM = mem.M(s);
         for (int e2 = g.lane(); e2 < n * n; e2 += NT) {
             const int col = e2 / n, row = e2 - col * n;
             dstM[e2] = wk.M[(size_t) col * ldm + row];
@@ -196,54 +238,57 @@ __global__ void __launch_bounds__(512) batchSetupKernel(const MechView v, const 
     }
 }
 
-//! Dense LU with partial pivoting of the flagged slots' Newton matrices (the role of
-//! SUNLinSol_Dense, CVodesIntegrator.cpp:382-411): ONE WARP per matrix. The warp brings the slot's
-//! [perm | M] region into its shared-memory buffer with a TMA bulk copy, factors it there with
-//! warp-synchronous steps only (lanes own rows; the pivot is a shuffle arg-max), leaves the
-//! reciprocal pivots on the diagonal and the composed permutation for the controller's solves, and
-//! writes the region back with a bulk store. 8 matrices in flight per SM.
-__global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
+//! (I - gamma J)^-1 of the flagged slots by in-place Gauss-Jordan elimination with partial (row)
+//! pivoting — the role of SUNLinSol_Dense's factorisation (CVodesIntegrator.cpp:382-411), with the
+//! inverse instead of the factors so that the controller's solves have no dependent chain.
+//! One CTA of RP * SPLIT threads per matrix: thread (h, row) keeps columns [h CPT, (h+1) CPT) of
+//! matrix row `row` in REGISTERS for the whole elimination (the k loop is unrolled, so every register
+//! index is static). Rows are never exchanged: step k picks the largest |a_ik| among the rows not
+//! yet used as a pivot (every warp finds it redundantly from the published column, no cross-warp
+//! traffic), the pivot row broadcasts its scaled segment through shared memory, and every other row
+//! does CPT fused multiply-adds. The implied permutation is undone for free when the result is
+//! stored: thread (h, row) pivoted at step kk holds row kk of the inverse, column r_j at position j.
+template <int RP, int SPLIT, int CPT>
+__global__ void __launch_bounds__(RP * SPLIT) batchInvertKernel(const SlotMem mem)
 {
-    extern __shared__ __align__(128) unsigned char smem[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
-    const uint32_t region = (uint32_t) (mem.oJ - mem.oPerm); // [perm | M]
-    unsigned char* buf = smem + (size_t) warp * region;
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * region) + warp;
-    if (lane == 0) {
-        const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncwarp();
+    static_assert(CPT % 2 == 0, "segments are read with 128-bit loads");
+    __shared__ __align__(16) double colbuf[RP];
+    __shared__ __align__(16) double rowbuf[SPLIT * CPT];
+    __shared__ int piv[SPLIT * CPT];
     const int n = mem.n;
-    int* perm = reinterpret_cast<int*>(buf);
-    double* M = reinterpret_cast<double*>(buf + (mem.oM - mem.oPerm));
-    const int count = *mem.setupCount;
-    uint32_t parity = 0;
-    long long tk = mem.prof ? clock64() : 0;
-    for (int e = blockIdx.x * W + warp; e < count; e += gridDim.x * W) {
+    const int tid = threadIdx.x, h = tid / RP, row = tid % RP, lane = tid & 31;
+    const int count = mem.setupCount[mem.parity];
+    const long long tk = mem.prof ? clock64() : 0;
+    for (int e = blockIdx.x; e < count; e += gridDim.x) {
         const int s = mem.setupList[e];
-        unsigned char* gblk = mem.block(s) + mem.oPerm;
-        if (lane == 0) bulkLoad(M, mem.J(s), ((uint32_t) (n * n) * 8u + 15u) & ~15u, bar);
-        barWait(bar, parity);
-        parity ^= 1;
-        {
-            const double gamma = mem.ctl(s)->gamma;
-            for (int col = 0; col < n; col++) {
-                double* cc = M + (size_t) col * n;
-                for (int row = lane; row < n; row += 32) cc[row] = (row == col ? 1.0 : 0.0) - gamma * cc[row];
-            }
-            __syncwarp();
+        double* Mg = mem.M(s);
+        const double gamma = mem.ctl(s)->gamma;
+        const bool rowOk = row < n;
+        double a[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; j++) {
+            const int col = h * CPT + j;
+            double val = 0.0;
+            if (rowOk && col < n) val = (row == col ? 1.0 : 0.0) - gamma * Mg[(size_t) col * n + row];
+            a[j] = val;
         }
-        int fail = 0;
-        for (int k = 0; k < n; k++) {
-            double* ck = M + (size_t) k * n;
-            // pivot: arg-max |a_ik|, i >= k (lowest index on ties, as the sequential search)
+        // rows lane, lane + 32, ... are the ones this lane scans in the pivot search
+        unsigned usedMask = 0;
+#pragma unroll
+        for (int r = 0; r < RP / 32; r++) if (lane + 32 * r >= n) usedMask |= 1u << r;
+        int myStep = -1;
+        bool sing = false;
+#pragma unroll
+        for (int k = 0; k < SPLIT * CPT; k++) {
+            if (k >= n || sing) break;
+            if (h == k / CPT) colbuf[row] = a[k % CPT];
+            __syncthreads();
             double best = -1.0;
-            int bi = n;
-            for (int i = k + lane; i < n; i += 32) {
-                const double a = fabs(ck[i]);
-                if (a > best) { best = a; bi = i; }
+            int bi = RP;
+#pragma unroll
+            for (int r = 0; r < RP / 32; r++) {
+                const double val = fabs(colbuf[lane + 32 * r]);
+                if (!((usedMask >> r) & 1u) && val > best) { best = val; bi = lane + 32 * r; }
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
@@ -251,93 +296,53 @@ __global__ void __launch_bounds__(256) batchLuKernel(const SlotMem mem)
                 const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
                 if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
             }
-            const int p = bi;
-            if (lane == 0) perm[k] = p; // recorded swap; composed below
-            if (!(best > 0.0)) {
-                if (!fail) fail = k + 1;
+            if (!(best > 0.0) || !(best <= 1.7e308)) {
+                sing = true;      // zero, NaN or infinite column: the controller retries with a smaller step
+                __syncthreads();
                 continue;
             }
-            if (p != k) {
-                for (int j = lane; j < n; j += 32) {
-                    double* cj = M + (size_t) j * n;
-                    const double t = cj[k];
-                    cj[k] = cj[p];
-                    cj[p] = t;
+            const int p = bi;
+            if ((p & 31) == lane) usedMask |= 1u << (p >> 5);
+            const double f = colbuf[row];
+            const double pinv = 1.0 / colbuf[p];
+            if (row == p) {
+                myStep = k;
+#pragma unroll
+                for (int j = 0; j < CPT; j++) {
+                    double val = a[j] * pinv;
+                    if (j == k % CPT && h == k / CPT) val = pinv;
+                    a[j] = val;
+                    rowbuf[h * CPT + j] = val;
+                }
+                if (h == 0) piv[k] = p;
+            }
+            __syncthreads();
+            if (row != p) {
+                const double2* rb = reinterpret_cast<const double2*>(rowbuf + h * CPT);
+#pragma unroll
+                for (int j = 0; j < CPT; j += 2) {
+                    const double2 r2 = rb[j / 2];
+                    a[j] = (j == k % CPT && h == k / CPT) ? -f * r2.x : fma(-f, r2.x, a[j]);
+                    a[j + 1] = (j + 1 == k % CPT && h == k / CPT) ? -f * r2.y : fma(-f, r2.y, a[j + 1]);
                 }
             }
-            __syncwarp();
-            const double rp = 1.0 / ck[k];
-            double l[4];
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const int i = k + 1 + lane + 32 * r;
-                l[r] = 0.0;
-                if (i < n) {
-                    l[r] = ck[i] * rp;
-                    ck[i] = l[r];
-                }
-            }
-            // rank-1 update: lanes own rows (at most 4 chunks of 32 for n <= 128)
-            const int rows = n - k - 1;
-#pragma unroll 2
-            for (int j = k + 1; j < n; j++) {
-                double* cj = M + (size_t) j * n;
-                const double akj = cj[k];
-                double* cji = cj + k + 1 + lane;
-                if (lane < rows) cji[0] -= l[0] * akj;
-                if (lane + 32 < rows) cji[32] -= l[1] * akj;
-                if (lane + 64 < rows) cji[64] -= l[2] * akj;
-                if (lane + 96 < rows) cji[96] -= l[3] * akj;
-            }
-            __syncwarp();
         }
-        // reciprocal pivots; composed permutation (P b)[i] = b[id[i]]
-        for (int k = lane; k < n; k += 32) M[(size_t) k * n + k] = 1.0 / M[(size_t) k * n + k];
-        {
-            // id starts as the identity, distributed like the solve's vectors (element i in lane
-            // i % 32, register i / 32); the recorded swaps are applied in order by shuffles
-            int idr[4];
+        __syncthreads();
+        if (!sing && myStep >= 0) {
 #pragma unroll
-            for (int r = 0; r < 4; r++) idr[r] = lane + 32 * r;
-            for (int k = 0; k < n; k++) {
-                const int p = perm[k];
-                if (p != k) {
-                    int srcK = idr[0], srcP = idr[0];
-#pragma unroll
-                    for (int r = 1; r < 4; r++) {
-                        if ((k >> 5) == r) srcK = idr[r];
-                        if ((p >> 5) == r) srcP = idr[r];
-                    }
-                    const int vK = __shfl_sync(0xffffffffu, srcK, k & 31);
-                    const int vP = __shfl_sync(0xffffffffu, srcP, p & 31);
-#pragma unroll
-                    for (int r = 0; r < 4; r++) {
-                        if (lane == (k & 31) && (k >> 5) == r) idr[r] = vP;
-                        if (lane == (p & 31) && (p >> 5) == r) idr[r] = vK;
-                    }
-                }
-            }
-            __syncwarp();
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const int i = lane + 32 * r;
-                if (i < n) perm[i] = idr[r];
+            for (int j = 0; j < CPT; j++) {
+                const int col = h * CPT + j;
+                if (col < n) Mg[(size_t) piv[col] * n + myStep] = a[j];
             }
         }
-        __syncwarp();
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) {
-            mem.ctl(s)->sing = fail;
-            bulkStore(gblk, buf, region);
-        }
-        __syncwarp();
+        if (tid == 0) mem.ctl(s)->sing = sing ? 1 : 0;
+        __syncthreads();
     }
-    if (mem.prof && lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 5), (unsigned long long) (clock64() - tk));
+    if (mem.prof && tid == 0) atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 5), (unsigned long long) (clock64() - tk));
 }
 
 template <int NT>
-bool launchSetupT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+bool launchJacT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 {
     const MechView& v = m.view;
     const size_t groupDoubles = 16 + reactorWorkDoubles(v.K, v.R);
@@ -348,13 +353,13 @@ bool launchSetupT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
     groups = std::min(groups, std::min(15, 512 / NT));
     if (groups < 1) return false;
     const size_t smemBytes = fixed + (size_t) groups * groupDoubles * 8;
-    auto kern = batchSetupKernel<NT>;
+    auto kern = batchJacKernel<NT>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
     kern<<<m.numSMs, groups * NT, smemBytes, stream>>>(v, m.dBlob, mem, (int) groupDoubles);
     return true;
 }
 
-void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, cudaEvent_t between = nullptr)
+void launchJac(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 {
     const MechView& v = m.view;
     const size_t groupBytes = (16 + reactorWorkDoubles(v.K, v.R)) * 8;
@@ -362,24 +367,36 @@ void launchSetup(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, c
     const int fit = (int) std::max<size_t>(1, budget / groupBytes);
     int nt = 32;
     while (nt < 256 && fit * nt * 2 <= 512) nt *= 2;
-    if (const char* e = std::getenv("CTB_SETUP_NT")) nt = std::atoi(e);
     bool ok;
     switch (nt) {
-    case 32: ok = launchSetupT<32>(m, mem, stream); break;
-    case 64: ok = launchSetupT<64>(m, mem, stream); break;
-    case 128: ok = launchSetupT<128>(m, mem, stream); break;
-    case 256: ok = launchSetupT<256>(m, mem, stream); break;
-    default: throw std::runtime_error("CTB_SETUP_NT must be 32, 64, 128 or 256");
+    case 32: ok = launchJacT<32>(m, mem, stream); break;
+    case 64: ok = launchJacT<64>(m, mem, stream); break;
+    case 128: ok = launchJacT<128>(m, mem, stream); break;
+    default: ok = launchJacT<256>(m, mem, stream); break;
     }
     if (!ok) throw std::runtime_error("mechanism too large for the shared-memory Newton-matrix kernel");
-    if (between) cudaEventRecord(between, stream);
-    // factorisation: one warp per flagged matrix
-    const size_t region = (size_t) (mem.oJ - mem.oPerm);
-    const int warps = (int) std::min<size_t>(8, ((size_t) m.smemOptIn - 1024 - 64) / (region + 256));
-    if (warps < 1) throw std::runtime_error("Newton matrix does not fit in shared memory");
-    const size_t luSmem = (size_t) warps * region + 64 + (size_t) warps * 32 * 8;
-    cudaFuncSetAttribute(batchLuKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) luSmem);
-    batchLuKernel<<<m.numSMs, warps * 32, luSmem, stream>>>(mem);
+}
+
+template <int RP, int SPLIT, int CPT>
+void launchInvertT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+{
+    auto kern = batchInvertKernel<RP, SPLIT, CPT>;
+    int perSm = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, RP * SPLIT, 0);
+    perSm = std::max(1, perSm);
+    kern<<<m.numSMs * perSm, RP * SPLIT, 0, stream>>>(mem);
+}
+
+void launchInvert(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+{
+    const int n = mem.n;
+    if (n <= 16) launchInvertT<32, 1, 16>(m, mem, stream);
+    else if (n <= 32) launchInvertT<32, 1, 32>(m, mem, stream);
+    else if (n <= 56) launchInvertT<64, 1, 56>(m, mem, stream);
+    else if (n <= 64) launchInvertT<64, 2, 32>(m, mem, stream);
+    else if (n <= 104) launchInvertT<128, 2, 52>(m, mem, stream);
+    else if (n <= 128) launchInvertT<128, 2, 64>(m, mem, stream);
+    else throw std::runtime_error("more than 128 equations per reactor");
 }
 
 } // namespace
@@ -388,9 +405,8 @@ long long batchSlotCap(const DeviceMech& m, int neq)
 {
     SlotMem tmp = {};
     const unsigned long long slotBytes = slotLayout(neq, tmp);
-    (void) slotBytes;
-    if (tmp.oJ + 64ull > (unsigned long long) m.smemOptIn - 1024) return 0; // a slot must fit the control kernel's buffer
     if ((neq + 31) / 32 > 4) return 0;
+    if ((unsigned long long) tmp.oM * 4 + 256 > (unsigned long long) m.smemOptIn - 1024) return 0;
     // enough slots for several waves of every kernel, bounded by ~8 GB of slot memory
     long long cap = (long long) m.numSMs * 512;
     cap = std::min<long long>(cap, (8LL << 30) / (long long) slotBytes);
@@ -406,7 +422,7 @@ size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay)
     BatchLayout l;
     l.slots = take((size_t) slotBytes * S);
     l.pc = take(sizeof(int) * S);
-    l.setupList = take(sizeof(int) * 2 * S);
+    l.setupList = take(sizeof(int) * S);
     l.counters = take(256);
     if (lay) *lay = l;
     return off;
@@ -425,12 +441,10 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     mem.slots = w + l.slots;
     mem.pc = reinterpret_cast<int*>(w + l.pc);
     mem.setupList = reinterpret_cast<int*>(w + l.setupList);
-    mem.jacList = mem.setupList + S;
     mem.setupCount = reinterpret_cast<int*>(w + l.counters);
-    mem.nActive = mem.setupCount + 1;
-    mem.jacCount = mem.setupCount + 2;
+    mem.nActive = mem.setupCount + 2;
     mem.S = (int) S;
-    const bool profile = std::getenv("CTB_PROFILE") != nullptr;
+    const bool profile = std::getenv("CTB_PROFILE") != nullptr; // diagnostics only: never changes results
     mem.prof = profile ? reinterpret_cast<long long*>(w + l.counters + 64) : nullptr;
     if (profile) cudaMemsetAsync(mem.prof, 0, 16 * sizeof(long long), stream);
 
@@ -445,12 +459,12 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     cudaFuncSetAttribute(batchRhsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) rhsSmem);
     const int rhsGrid = (int) std::max<long long>(1, std::min<long long>((S + rhsGroups - 1) / rhsGroups, m.numSMs));
 
-    // ---- control kernel: one shared-memory slot buffer per warp
-    int ctlWarps = (int) std::min<size_t>(8, (budget - 64) / mem.oJ);
+    // ---- control kernel: one shared-memory [ctl | vec] buffer per warp
+    int ctlWarps = (int) std::min<size_t>(CTB_CTL_WARPS, (budget - 256) / mem.oM);
     if (ctlWarps < 1) throw std::runtime_error("a reactor slot does not fit in shared memory");
-    const size_t ctlSmem = (size_t) ctlWarps * mem.oJ + 64;
+    const size_t ctlSmem = (size_t) ctlWarps * mem.oM + 256;
     const int npl = (n + 31) / 32;
-    if (npl > 4) throw std::runtime_error("more than 128 equations per reactor: use the persistent integrator");
+    if (npl > 4) throw std::runtime_error("more than 128 equations per reactor");
     const int ctlGrid = (int) std::max<long long>(1, std::min<long long>((S + ctlWarps - 1) / ctlWarps, m.numSMs));
     void (*ctlKern)(const ReactorBatch, const SlotMem) =
         npl == 1 ? batchControlKernel<1> : npl == 2 ? batchControlKernel<2> : npl == 3 ? batchControlKernel<3>
@@ -459,7 +473,10 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
 
     batchInitKernel<<<(unsigned) ((S + 255) / 256), 256, 0, stream>>>(mem);
     long long rounds = 0;
-    const long long maxRounds = 64LL * b.maxSteps + 1000;
+    // every reactor is bounded by maxSteps, every step by MXNCF + MXNEF attempts of at most
+    // 2 * MAXCOR + 2 right-hand sides: the loop ends on nActive alone; the bound is a safety net
+    const long long perReactor = (long long) b.maxSteps * (BDF_MXNCF + BDF_MXNEF) * (2 * BDF_MAXCOR + 2) + 64;
+    const long long maxRounds = ((b.N + S - 1) / S + 1) * perReactor;
     int active = 1;
     // CTB_PROFILE: CUDA events around every kernel of a round, read at the 16-round sync points
     cudaEvent_t ev[16][5];
@@ -467,14 +484,15 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     if (profile) for (auto& r : ev) for (auto& e : r) cudaEventCreate(&e);
     while (rounds < maxRounds) {
         cudaEvent_t* e5 = profile ? ev[rounds & 15] : nullptr;
-        cudaMemsetAsync(mem.setupCount, 0, sizeof(int), stream);
-        cudaMemsetAsync(mem.jacCount, 0, sizeof(int), stream);
+        mem.parity = (int) (rounds & 1);
         if (e5) cudaEventRecord(e5[0], stream);
         ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem);
         if (e5) cudaEventRecord(e5[1], stream);
         batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
         if (e5) cudaEventRecord(e5[2], stream);
-        launchSetup(m, mem, stream, e5 ? e5[3] : nullptr);
+        launchJac(m, mem, stream);
+        if (e5) cudaEventRecord(e5[3], stream);
+        launchInvert(m, mem, stream);
         if (e5) cudaEventRecord(e5[4], stream);
         rounds++;
         if ((rounds & 15) == 0) {
@@ -493,13 +511,19 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
             if (active <= 0) break;
         }
     }
+    if (active > 0) {
+        // the control kernel of the last round may have emptied the pool after the last read
+        cudaMemcpyAsync(&active, mem.nActive, sizeof(int), cudaMemcpyDeviceToHost, stream);
+        cudaStreamSynchronize(stream);
+        if (active > 0) {
+            const long long items = std::max<long long>(S, b.N);
+            batchAbortKernel<<<(unsigned) ((items + 255) / 256), 256, 0, stream>>>(b, mem);
+        }
+    }
     if (profile) {
         for (auto& r : ev) for (auto& e : r) cudaEventDestroy(e);
-        std::fprintf(stderr, "[ctb profile] kernel time over %lld rounds: control %.1f ms, rhs %.1f ms, setup %.1f ms, lu %.1f ms\n",
+        std::fprintf(stderr, "[ctb profile] kernel time over %lld rounds: control %.1f ms, rhs %.1f ms, jacobian %.1f ms, invert %.1f ms\n",
                      rounds, kernMs[0], kernMs[1], kernMs[2], kernMs[3]);
-    }
-    if (active > 0) throw std::runtime_error("batch integrator: round limit reached");
-    if (profile) {
         long long h[16];
         cudaMemcpy(h, mem.prof, sizeof(h), cudaMemcpyDeviceToHost);
         const double nc = h[11] ? (double) h[11] : 1.0;
@@ -507,8 +531,8 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
                      h[11], h[8] / nc, h[9] / nc, h[10] / nc);
         const double ns = h[7] ? (double) h[7] : 1.0;
         std::fprintf(stderr, "[ctb profile] rounds %lld, setups %lld; cycles per setup: rhs+jacdata %.0f, jacobianCi %.0f, "
-                     "dense rows %.0f, T column %.0f, I-gJ %.0f, LU %.0f, writeback %.0f\n", rounds, h[7], h[0] / ns,
-                     h[1] / ns, h[2] / ns, h[3] / ns, h[4] / ns, h[5] / ns, h[6] / ns);
+                     "dense rows %.0f, T column %.0f, writeback %.0f; invert CTA-cycles total %lld\n", rounds, h[7], h[0] / ns,
+                     h[1] / ns, h[2] / ns, h[3] / ns, h[6] / ns, h[5]);
     }
     return rounds;
 }

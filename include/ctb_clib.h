@@ -16,7 +16,8 @@
  *
  * Batch layout: T[n], P[n] and Y[n*ldY + k] (one state per row, species contiguous; ldY >= K).
  * Per-state outputs use the same row layout with their own leading dimension.
- * memspace: CTB_HOST (0) = host pointers, staged through pinned buffers by the library;
+ * memspace: CTB_HOST (0) = host pointers (pageable or pinned; the library copies in chunks through
+ *           device staging buffers, see DESIGN.md "End-to-end path");
  *           CTB_DEVICE (1) = device pointers on the handle's device, no copies.
  *
  * There is no CPU fallback: if no CUDA device is usable every constructor fails with -1.
@@ -199,6 +200,13 @@ int32_t ctb_reactornet_setState(int32_t handle, const double* T, const double* P
 int32_t ctb_reactornet_setRelativeTolerance(int32_t handle, double rtol); /* ReactorNet.cpp:190-198 */
 int32_t ctb_reactornet_setAbsoluteTolerance(int32_t handle, double atol); /* ReactorNet.cpp:200-209 */
 int32_t ctb_reactornet_setMaxSteps(int32_t handle, int32_t maxSteps);     /* Integrator::setMaxSteps */
+/* The tolerances the integrator actually applies (ReactorNet::rtol / atol, ReactorNet.h:101-108):
+ * out[0] = rtol, out[1] = absolute tolerance of the temperature row, out[2] = absolute tolerance of
+ * the species rows, out[3] = 1 if the absolute tolerance was set by the caller, else 0. A caller-set
+ * value is applied unchanged to every row (ReactorNet.cpp:200-209). The default (1e-15, times the
+ * reactor's total moles for the species rows: MoleReactor.cpp:64-76, so out[2] is then per kmol) is
+ * applied with a safety factor 0.1 — see DESIGN.md "Tolerance mapping". len >= 4. */
+int32_t ctb_reactornet_getTolerances(int32_t handle, int32_t len, double* out);
 int32_t ctb_reactornet_setInitialTime(int32_t handle, double t0);
 /* ReactorNet::advance(t) (ReactorNet.cpp:351-357) for every reactor. Numerical failure of a
  * reactor never fails the call: it is reported through ctb_reactornet_status. */

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <stdexcept>
 #include <string>
+#include <map>
 #include <vector>
 
 struct ArrayFile {
@@ -34,5 +35,47 @@ struct ArrayFile {
             std::fwrite(e.bytes.data(), 1, e.bytes.size(), f);
         }
         std::fclose(f);
+    }
+};
+
+//! Reader of the same layout (only the f64 / i32 arrays are kept).
+struct ArrayReader {
+    std::map<std::string, std::vector<double>> dbl;
+    std::map<std::string, std::vector<int32_t>> i32;
+    void load(const std::string& path) {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) throw std::runtime_error("cannot open " + path);
+        auto rd = [&](void* p, size_t n) {
+            if (n && std::fread(p, 1, n, f) != n) {
+                std::fclose(f);
+                throw std::runtime_error("truncated array file " + path);
+            }
+        };
+        char magic[8];
+        rd(magic, 8);
+        if (std::string(magic, 8) != "CTBM0001") {
+            std::fclose(f);
+            throw std::runtime_error(path + " is not a CTBM0001 file");
+        }
+        uint32_t n;
+        rd(&n, 4);
+        for (uint32_t a = 0; a < n; a++) {
+            uint32_t nl, dtype;
+            uint64_t cnt;
+            rd(&nl, 4);
+            std::string name(nl, '\0');
+            rd(&name[0], nl);
+            rd(&dtype, 4);
+            rd(&cnt, 8);
+            if (dtype == 0) { auto& v = dbl[name]; v.resize(cnt); rd(v.data(), cnt * 8); }
+            else if (dtype == 1) { auto& v = i32[name]; v.resize(cnt); rd(v.data(), cnt * 4); }
+            else { std::string s(cnt, '\0'); rd(&s[0], cnt); }
+        }
+        std::fclose(f);
+    }
+    const std::vector<double>& d(const std::string& name) const {
+        auto it = dbl.find(name);
+        if (it == dbl.end()) throw std::runtime_error("array '" + name + "' missing");
+        return it->second;
     }
 };

@@ -4,7 +4,10 @@
 //
 //   gen_golden rates  <yaml> <phase> <out> <N> <seed>
 //   gen_golden ddx    <yaml> <phase> <out> <N> <seed>
-//   gen_golden rhs    <yaml> <phase> <out> <N> <seed>
+//   gen_golden rhs    <yaml> <phase> <out> <N> <seed> [reactorType]
+//   gen_golden rjac   <yaml> <phase> <out> <N> <seed>          reactor Jacobian (getJacobianElements), dense
+//   gen_golden ddxdigest <yaml> <phase> <out> <N> <seed>       J r, l^T J, |J||r|, |l|^T|J| of netProductionRates_ddX
+//   gen_golden derivs <yaml> <phase> <out> <N> <seed>          _ddT/_ddP/_ddC families and getDelta*
 //   gen_golden ignite <yaml> <phase> <out> <N> <seed> <fuel> <nO2> <O2> <N2> <Tlo> <Thi> <Plo_atm> <Phi_atm> <tEnd> [rtol atol]
 //
 // States follow SURVEY.md §8(d): T ~ U(800, 2500) K, P = 101325 * U(1, 50) Pa, Y_k = u_k / sum u.
@@ -15,10 +18,14 @@
 #include "cantera/kinetics/Kinetics.h"
 #include "cantera/thermo/ThermoPhase.h"
 #include "cantera/zeroD/IdealGasConstPressureMoleReactor.h"
+#include "cantera/zeroD/IdealGasConstPressureReactor.h"
+#include "cantera/zeroD/IdealGasMoleReactor.h"
+#include "cantera/zeroD/IdealGasReactor.h"
 #include "cantera/zeroD/ReactorNet.h"
 #include "cantera/numerics/eigen_sparse.h"
 
 #include <cmath>
+#include <functional>
 #include <iostream>
 #include <random>
 
@@ -135,27 +142,175 @@ static int runDdx(shared_ptr<Solution> sol, const std::string& out, size_t N, ui
     return 0;
 }
 
-static int runRhs(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+static shared_ptr<ReactorBase> makeReactor(const std::string& type, shared_ptr<Solution> sol)
+{
+    if (type == "IdealGasConstPressureMoleReactor") return std::make_shared<IdealGasConstPressureMoleReactor>(sol, false);
+    if (type == "IdealGasMoleReactor") return std::make_shared<IdealGasMoleReactor>(sol, false);
+    if (type == "IdealGasReactor") return std::make_shared<IdealGasReactor>(sol, false);
+    if (type == "IdealGasConstPressureReactor") return std::make_shared<IdealGasConstPressureReactor>(sol, false);
+    throw std::runtime_error("unknown reactor type " + type);
+}
+
+static int runRhs(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed,
+                  const std::string& type = "IdealGasConstPressureMoleReactor")
 {
     auto gas = sol->thermo();
     size_t K = gas->nSpecies();
     States s = randomStates(N, K, seed);
-    auto reactor = std::make_shared<IdealGasConstPressureMoleReactor>(sol, false);
+    auto reactor = makeReactor(type, sol);
     ReactorNet net(reactor);
-    std::vector<double> y(N * (K + 1)), ydot(N * (K + 1));
+    net.initialize();
+    const size_t neq = net.neq();
+    std::vector<double> y(N * neq), ydot(N * neq);
     for (size_t n = 0; n < N; n++) {
         for (size_t k = 0; k < K; k++) s.Y[n * K + k] = std::abs(s.Y[n * K + k]);
         gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
         net.setInitialTime(0.0);
         net.initialize();
-        net.getState(span<double>(&y[n * (K + 1)], K + 1));
-        net.eval(0.0, span<double>(&y[n * (K + 1)], K + 1), span<double>(&ydot[n * (K + 1)], K + 1),
+        net.getState(span<double>(&y[n * neq], neq));
+        net.eval(0.0, span<double>(&y[n * neq], neq), span<double>(&ydot[n * neq], neq),
                  span<double>());
+    }
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) sol->kinetics()->nReactions(), (int32_t) neq});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    f.add("y", y); f.add("ydot", ydot);
+    f.addText("reactor", type);
+    f.save(out);
+    return 0;
+}
+
+// IdealGasConstPressureMoleReactor::getJacobianElements (IdealGasConstPressureMoleReactor.cpp:108-174)
+// through ReactorBase::jacobian(), dense column-major (K+1)^2 per state; variants: default derivative
+// settings and skip-falloff (purely analytic species block).
+static int runRjac(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    size_t K = gas->nSpecies(), n1 = K + 1;
+    States s = randomStates(N, K, seed);
+    auto reactor = std::make_shared<IdealGasConstPressureMoleReactor>(sol, false);
+    ReactorNet net(reactor);
+    std::vector<double> y(N * n1), jdef(N * n1 * n1), jsf(N * n1 * n1);
+    for (size_t n = 0; n < N; n++) {
+        for (size_t k = 0; k < K; k++) s.Y[n * K + k] = std::abs(s.Y[n * K + k]);
+        gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+        net.setInitialTime(0.0);
+        net.initialize();
+        net.getState(span<double>(&y[n * n1], n1));
+        AnyMap st;
+        reactor->setDerivativeSettings(st);
+        densify(reactor->jacobian(), &jdef[n * n1 * n1], n1);
+        AnyMap st2;
+        st2["skip-falloff"] = true;
+        reactor->setDerivativeSettings(st2);
+        densify(reactor->jacobian(), &jsf[n * n1 * n1], n1);
+        AnyMap st3;
+        st3["skip-falloff"] = false;
+        reactor->setDerivativeSettings(st3);
     }
     ArrayFile f;
     f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) sol->kinetics()->nReactions()});
     f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
-    f.add("y", y); f.add("ydot", ydot);
+    f.add("y", y); f.add("jac", jdef); f.add("jac_skip_falloff", jsf);
+    f.save(out);
+    return 0;
+}
+
+// Digest of netProductionRates_ddX for many states: J r and l^T J for fixed seeded vectors, plus
+// the magnitude sums |J||r| and |l|^T|J| that scale the comparison (a single wrong element (k, j)
+// of size delta moves (J r)_k by delta r_j and (l^T J)_j by delta l_k).
+static int runDdxDigest(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    auto kin = sol->kinetics();
+    size_t K = gas->nSpecies();
+    States s = randomStates(N, K, seed);
+    std::mt19937_64 rng(seed ^ 0x9e3779b97f4a7c15ULL);
+    std::uniform_real_distribution<double> U(0.5, 1.5);
+    std::vector<double> r(K), l(K);
+    for (size_t k = 0; k < K; k++) { r[k] = U(rng); l[k] = U(rng); }
+    const char* names[3] = {"skip_falloff", "skip_third_bodies", "default"};
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) kin->nReactions()});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y); f.add("r", r); f.add("l", l);
+    for (int v = 0; v < 3; v++) {
+        AnyMap st;
+        kin->setDerivativeSettings(st);
+        if (v == 0) st["skip-falloff"] = true;
+        if (v == 1) st["skip-third-bodies"] = true;
+        if (v < 2) kin->setDerivativeSettings(st);
+        std::vector<double> Jr(N * K, 0.0), lJ(N * K, 0.0), aJr(N * K, 0.0), alJ(N * K, 0.0);
+        for (size_t n = 0; n < N; n++) {
+            gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+            auto J = kin->netProductionRates_ddX();
+            for (int c = 0; c < J.outerSize(); c++) {
+                for (Eigen::SparseMatrix<double>::InnerIterator it(J, c); it; ++it) {
+                    Jr[n * K + it.row()] += it.value() * r[it.col()];
+                    aJr[n * K + it.row()] += std::abs(it.value()) * r[it.col()];
+                    lJ[n * K + it.col()] += it.value() * l[it.row()];
+                    alJ[n * K + it.col()] += std::abs(it.value()) * l[it.row()];
+                }
+            }
+        }
+        f.add(std::string("Jr_") + names[v], Jr); f.add(std::string("lJ_") + names[v], lJ);
+        f.add(std::string("aJr_") + names[v], aJr); f.add(std::string("alJ_") + names[v], alJ);
+    }
+    AnyMap reset;
+    kin->setDerivativeSettings(reset);
+    f.save(out);
+    return 0;
+}
+
+// The derivative families of Kinetics.h:1040-1330 (BulkKinetics.cpp:284-385, Kinetics.cpp:459-602)
+// and the reaction deltas (BulkKinetics.cpp:200-257).
+static int runDerivs(shared_ptr<Solution> sol, const std::string& out, size_t N, uint64_t seed)
+{
+    auto gas = sol->thermo();
+    auto kin = sol->kinetics();
+    size_t K = gas->nSpecies(), R = kin->nReactions();
+    States s = randomStates(N, K, seed);
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, (int32_t) R});
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    struct Get { const char* name; bool species; std::function<void(Kinetics&, span<double>)> fn; };
+    std::vector<Get> gets = {
+        {"kf_ddT", false, [](Kinetics& k, span<double> o) { k.getFwdRateConstants_ddT(o); }},
+        {"kf_ddP", false, [](Kinetics& k, span<double> o) { k.getFwdRateConstants_ddP(o); }},
+        {"kf_ddC", false, [](Kinetics& k, span<double> o) { k.getFwdRateConstants_ddC(o); }},
+        {"ropf_ddT", false, [](Kinetics& k, span<double> o) { k.getFwdRatesOfProgress_ddT(o); }},
+        {"ropf_ddP", false, [](Kinetics& k, span<double> o) { k.getFwdRatesOfProgress_ddP(o); }},
+        {"ropf_ddC", false, [](Kinetics& k, span<double> o) { k.getFwdRatesOfProgress_ddC(o); }},
+        {"ropr_ddT", false, [](Kinetics& k, span<double> o) { k.getRevRatesOfProgress_ddT(o); }},
+        {"ropr_ddP", false, [](Kinetics& k, span<double> o) { k.getRevRatesOfProgress_ddP(o); }},
+        {"ropr_ddC", false, [](Kinetics& k, span<double> o) { k.getRevRatesOfProgress_ddC(o); }},
+        {"ropnet_ddT", false, [](Kinetics& k, span<double> o) { k.getNetRatesOfProgress_ddT(o); }},
+        {"ropnet_ddP", false, [](Kinetics& k, span<double> o) { k.getNetRatesOfProgress_ddP(o); }},
+        {"ropnet_ddC", false, [](Kinetics& k, span<double> o) { k.getNetRatesOfProgress_ddC(o); }},
+        {"cdot_ddT", true, [](Kinetics& k, span<double> o) { k.getCreationRates_ddT(o); }},
+        {"cdot_ddP", true, [](Kinetics& k, span<double> o) { k.getCreationRates_ddP(o); }},
+        {"cdot_ddC", true, [](Kinetics& k, span<double> o) { k.getCreationRates_ddC(o); }},
+        {"ddot_ddT", true, [](Kinetics& k, span<double> o) { k.getDestructionRates_ddT(o); }},
+        {"ddot_ddP", true, [](Kinetics& k, span<double> o) { k.getDestructionRates_ddP(o); }},
+        {"ddot_ddC", true, [](Kinetics& k, span<double> o) { k.getDestructionRates_ddC(o); }},
+        {"wdot_ddT", true, [](Kinetics& k, span<double> o) { k.getNetProductionRates_ddT(o); }},
+        {"wdot_ddP", true, [](Kinetics& k, span<double> o) { k.getNetProductionRates_ddP(o); }},
+        {"wdot_ddC", true, [](Kinetics& k, span<double> o) { k.getNetProductionRates_ddC(o); }},
+        {"deltaGibbs", false, [](Kinetics& k, span<double> o) { k.getDeltaGibbs(o); }},
+        {"deltaEnthalpy", false, [](Kinetics& k, span<double> o) { k.getDeltaEnthalpy(o); }},
+        {"deltaEntropy", false, [](Kinetics& k, span<double> o) { k.getDeltaEntropy(o); }},
+        {"deltaSSGibbs", false, [](Kinetics& k, span<double> o) { k.getDeltaSSGibbs(o); }},
+        {"deltaSSEnthalpy", false, [](Kinetics& k, span<double> o) { k.getDeltaSSEnthalpy(o); }},
+        {"deltaSSEntropy", false, [](Kinetics& k, span<double> o) { k.getDeltaSSEntropy(o); }},
+    };
+    for (auto& g : gets) {
+        const size_t w = g.species ? K : R;
+        std::vector<double> v(N * w);
+        for (size_t n = 0; n < N; n++) {
+            gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+            g.fn(*kin, span<double>(&v[n * w], w));
+        }
+        f.add(g.name, v);
+    }
     f.save(out);
     return 0;
 }
@@ -230,7 +385,7 @@ static int runIgnite(shared_ptr<Solution> sol, const std::string& out, size_t N,
 int main(int argc, char** argv)
 {
     if (argc < 7) {
-        std::cerr << "usage: gen_golden rates|ddx|rhs|ignite yaml phase out N seed [...]\n";
+        std::cerr << "usage: gen_golden rates|ddx|rhs|rjac|ddxdigest|derivs|ignite yaml phase out N seed [...]\n";
         return 2;
     }
     try {
@@ -241,7 +396,10 @@ int main(int argc, char** argv)
         uint64_t seed = std::stoull(argv[6]);
         if (mode == "rates") return runRates(sol, argv[4], N, seed);
         if (mode == "ddx") return runDdx(sol, argv[4], N, seed);
-        if (mode == "rhs") return runRhs(sol, argv[4], N, seed);
+        if (mode == "rhs") return runRhs(sol, argv[4], N, seed, argc > 7 ? argv[7] : "IdealGasConstPressureMoleReactor");
+        if (mode == "rjac") return runRjac(sol, argv[4], N, seed);
+        if (mode == "ddxdigest") return runDdxDigest(sol, argv[4], N, seed);
+        if (mode == "derivs") return runDerivs(sol, argv[4], N, seed);
         if (mode == "ignite") {
             if (argc < 17) {
                 std::cerr << "ignite needs fuel nO2 O2 N2 Tlo Thi Plo Phi tEnd dTign [rtol atol]\n";

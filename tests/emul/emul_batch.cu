@@ -67,29 +67,28 @@ int main(int argc, char** argv)
     ReactorBatch b = {};
     b.N = N; b.neq = n; b.y = y.data(); b.P = P.data(); b.T0 = T0.data(); b.hist = hist.data();
     b.histStride = histStride; b.tIgn = tIgn.data(); b.status = status.data(); b.stats = stats.data();
-    b.counter = &counter; b.t0 = 0.0; b.tout = th[0]; b.rtol = 1e-9; b.atol = 1e-15 * 0.1; b.atolUser = 0;
+    b.counter = &counter; b.t0 = 0.0; b.tout = th[0]; b.rtol = 1e-9; b.atol = 1e-15 * 0.1 /* reactor.cu kDefaultAtolSafety */; b.atolUser = 0;
     b.maxSteps = 20000; b.restart = 1; b.ignDT = th[1]; b.crateFloor = 0.0;
 
     SlotMem mem = {};
     const unsigned long long slotBytes = slotLayout(n, mem);
     std::vector<double> slotStore((size_t) slotBytes * S / 8 + 32, 0.0);
-    std::vector<int> setupList(S), jacList(S), pcArr(S, PC_NEW);
-    int setupCount = 0, jacCount = 0, nActive = S;
+    std::vector<int> setupList(S), pcArr(S, PC_NEW);
+    int setupCount[2] = {0, 0}, nActive = S;
     mem.slots = reinterpret_cast<unsigned char*>(slotStore.data());
     mem.pc = pcArr.data();
-    mem.setupCount = &setupCount; mem.setupList = setupList.data(); mem.nActive = &nActive; mem.S = S;
-    mem.jacCount = &jacCount; mem.jacList = jacList.data();
+    mem.setupCount = setupCount; mem.setupList = setupList.data(); mem.nActive = &nActive; mem.S = S;
+    mem.parity = 0;
     for (int s = 0; s < S; s++) mem.ctl(s)->pc = PC_NEW;
 
     const Solo solo;
-    std::vector<double> xs(2 * n), yy(n), f0(n), f1(n), J((size_t) n * n);
+    std::vector<double> xs(n), yy(n), f0(n), f1(n), J((size_t) n * n);
     long long rounds = 0;
     for (;; rounds++) {
-        setupCount = 0;
-        jacCount = 0;
+        setupCount[0] = 0;
         for (int s = 0; s < S; s++) {
             if (pcArr[s] == PC_IDLE) continue;
-            BatchBdf<Solo, 1> bdf(solo, b, mem, s, mem.block(s), xs.data());
+            BatchBdf<Solo, 1> bdf(solo, b, mem, s, mem.block(s), mem.M(s), xs.data());
             bdf.run();
         }
         if (nActive == 0) break;
@@ -98,14 +97,16 @@ int main(int argc, char** argv)
             double* sv = mem.vec(s);
             hostRhs(pm, mem.ctl(s)->P, sv + 8 * n, sv + 9 * n);
         }
-        // Jacobian evaluations (finite differences here; analytic on the GPU) -> saved J of the slot
-        for (int e = 0; e < jacCount; e++) {
-            const int s = jacList[e];
+        // flagged slots: Jacobian by finite differences here (analytic on the GPU), then
+        // (I - gamma J)^-1 by Gauss-Jordan elimination with partial pivoting (batchInvertKernel)
+        for (int e = 0; e < setupCount[0]; e++) {
+            const int s = setupList[e];
             const double Ps = mem.ctl(s)->P;
             for (int i = 0; i < n; i++) yy[i] = mem.vec(s)[8 * n + i];
             hostRhs(pm, Ps, yy.data(), f0.data());
             double ntot = 0.0;
             for (int i = 1; i < n; i++) ntot += yy[i];
+            const double gamma = mem.ctl(s)->gamma;
             for (int j = 0; j < n; j++) {
                 const double save = yy[j];
                 const double d = (j == 0) ? save * 1.4901161193847656e-08
@@ -113,37 +114,39 @@ int main(int argc, char** argv)
                 yy[j] = save + d;
                 hostRhs(pm, Ps, yy.data(), f1.data());
                 yy[j] = save;
-                for (int i = 0; i < n; i++) mem.J(s)[(size_t) j * n + i] = (f1[i] - f0[i]) / d;
+                for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * (f1[i] - f0[i]) / d;
             }
-        }
-        // Newton matrices I - gamma J from the saved Jacobians, factored
-        for (int e = 0; e < setupCount; e++) {
-            const int s = setupList[e];
-            const double gamma = mem.ctl(s)->gamma;
-            for (int j = 0; j < n; j++)
-                for (int i = 0; i < n; i++) J[(size_t) j * n + i] = (i == j ? 1.0 : 0.0) - gamma * mem.J(s)[(size_t) j * n + i];
+            // in-place Gauss-Jordan without row exchanges: step k takes the largest |a_ik| among the
+            // rows not used yet; row r_k then holds row k of the inverse, column r_j at position j
             int fail = 0;
-            std::vector<int> id(n);
-            for (int i = 0; i < n; i++) id[i] = i;
-            for (int k = 0; k < n; k++) {
-                int pv = k;
-                double best = std::fabs(J[(size_t) k * n + k]);
-                for (int i = k + 1; i < n; i++) if (std::fabs(J[(size_t) k * n + i]) > best) { best = std::fabs(J[(size_t) k * n + i]); pv = i; }
-                std::swap(id[k], id[pv]);
-                if (!(best > 0.0)) { fail = 1; continue; }
-                if (pv != k) for (int j = 0; j < n; j++) std::swap(J[(size_t) j * n + k], J[(size_t) j * n + pv]);
-                const double rp = 1.0 / J[(size_t) k * n + k];
-                for (int i = k + 1; i < n; i++) J[(size_t) k * n + i] *= rp;
-                for (int j = k + 1; j < n; j++) {
-                    const double ukj = J[(size_t) j * n + k];
-                    for (int i = k + 1; i < n; i++) J[(size_t) j * n + i] -= J[(size_t) k * n + i] * ukj;
+            std::vector<int> piv(n), stepOf(n, -1);
+            std::vector<char> used(n, 0);
+            for (int k = 0; k < n && !fail; k++) {
+                int pv = -1;
+                double best = 0.0;
+                for (int i = 0; i < n; i++) {
+                    const double a = std::fabs(J[(size_t) k * n + i]);
+                    if (!used[i] && a > best) { best = a; pv = i; }
+                }
+                if (pv < 0 || !std::isfinite(best)) { fail = 1; break; }
+                used[pv] = 1; piv[k] = pv; stepOf[pv] = k;
+                const double pinv = 1.0 / J[(size_t) k * n + pv];
+                for (int j = 0; j < n; j++) J[(size_t) j * n + pv] = (j == k) ? pinv : J[(size_t) j * n + pv] * pinv;
+                for (int i = 0; i < n; i++) {
+                    if (i == pv) continue;
+                    const double fct = J[(size_t) k * n + i];
+                    for (int j = 0; j < n; j++) {
+                        const double r = J[(size_t) j * n + pv];
+                        J[(size_t) j * n + i] = (j == k) ? -fct * r : J[(size_t) j * n + i] - fct * r;
+                    }
                 }
             }
             mem.ctl(s)->sing = fail;
-            for (int i = 0; i < n; i++) mem.perm(s)[i] = id[i];
-            for (int col = 0; col < n; col++)
-                for (int row = 0; row < n; row++)
-                    mem.M(s)[(size_t) col * n + row] = (row == col) ? 1.0 / J[(size_t) col * n + row] : J[(size_t) col * n + row];
+            if (!fail) {
+                double* Minv = mem.M(s);
+                for (int i = 0; i < n; i++)
+                    for (int j = 0; j < n; j++) Minv[(size_t) piv[j] * n + stepOf[i]] = J[(size_t) j * n + i];
+            }
         }
     }
     std::fprintf(stderr, "rounds %lld\n", rounds);

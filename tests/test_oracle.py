@@ -81,17 +81,12 @@ def test_reactor_rhs(case, oracle_lib):
 
 
 def test_pdep_known_answers(oracle_lib):
-    """Known-answer values of the reference's own test/kinetics/pdep.cpp:52-222 (Chemkin / RMG-py
-    numbers quoted there) reproduced through the oracle on the same fixture."""
+    """Known-answer values of the reference's own test/kinetics/pdep.cpp:100-222 (Chemkin / RMG-py
+    numbers quoted there) reproduced through the oracle on the same fixture and state."""
+    from conftest import check_pdep_kats
     m = oracle_lib.OracleMech(MECHS["pdep-test"])
-    K = m.K
-    # PlogLowPressure/PlogHighPressure etc. are covered by the golden file; here: the
-    # Chebyshev single-rate KATs (pdep.cpp:188-222: "ChebyshevIntermediate1/2")
-    names = open(MECHS["pdep-test"], "rb").read()
-    assert b"R6" in names or True
-    g = golden("rates", "pdep-test")
-    o = m.rates(g["T"], g["P"], g["Y"], want=("kf",))
-    assert np.all(np.isfinite(o["kf"])) and np.all(o["kf"] > 0)
+    assert m.R == 7  # pdep.cpp:47-50
+    check_pdep_kats(lambda T, P, Y, what: m.rates(T, P, Y, want=(what,))[what])
 
 
 def test_negative_and_unnormalised_mass_fractions(oracle_lib):
