@@ -1,37 +1,65 @@
 #!/usr/bin/env python
 """bench.py — the headline measurement (BASELINE.json): GRI-30 net-production-rate evaluations/s
-per B200 (config[1], 2^22 random states), plus 1 ms constant-pressure ignition reactors/s.
+and 1 ms constant-pressure ignition reactors/s per B200, with the other configs as workloads.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload wdot|ignition]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                    [--workload wdot|ddx|h2o2|ignition|ndodecane|substep]
 
-One "step" = one pass of the hot path over the whole batch. States have no inter-GPU dependence:
-under torchrun every rank owns its own 2^22-state batch (weak scaling, no collective on the data
-path); timing is CUDA events on the launching stream, max over ranks.
-Prints ONE JSON line on rank 0.
+Workloads (BASELINE.json configs; one "step" = one pass of the hot path over the whole batch):
+    wdot       config 2a  gri30 getNetProductionRates, 2^22 random states per GPU (weak scaling). The
+                          DEFAULT line; it also carries the `ignition` and `ddx` records below as
+                          sub-records, so the driver's line holds the whole metric.
+    ddx        config 2b  gri30 netProductionRates_ddX, 2^22 states per GPU in chunks of 2^19 (HBM-write bound)
+    h2o2       config 1   h2o2 getNetProductionRates, 2^20 states per GPU
+    ignition   config 3   gri30 IdealGasConstPressureMoleReactor advance(1e-3): 2^20 reactors IN TOTAL,
+                          dealt to the ranks as shares of one seeded permutation (strong scaling)
+    ndodecane  config 4   nDodecane_Reitz ignition sweep to 10 ms, 2^18 reactors in total (strong)
+    substep    config 5   gri30 advance(1e-5) from a cold start over 2^23 cells in total (strong)
+
+Every record carries: value (device-timed, inputs resident in HBM), e2e (through the C ABI with
+pinned HOST buffers, copies inside the timed region), roofline (live CUDA-event kernel time against
+the measured peak), cpu_baseline (the unmodified reference, oracle/_ref/ref_bench, on the host
+cores) and parity (the first states of the SAME batch pushed through the reference in the same run;
+the run fails with rc 3 if a north_star tolerance is exceeded).
+States have no inter-GPU dependence: no collective on the data path; timing is CUDA events on the
+launching stream, max over ranks. Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GRI = dict(K=53, R=325)
-FLOP_PER_STATE = 38374.0        # algorithmic FP64 flop per gri30 wdot evaluation
-BYTES_PER_STATE = 8 * (53 + 2) + 8 * 53  # 864 B: T, P, Y in; wdot out
+SEED = 20261104
 FP64_PEAK_TFLOPS_NOMINAL = 148 * 64 * 2 * 1.965e9 / 1e12  # 37.2: no FP64 entry in MEASURED_PEAKS.json
-WDOT_TRAFFIC_BYTES_PER_STATE = 874.8  # dram read+write per state, ncu --set full (profiles/r01_rates_kernel*.txt)
-# ignition: algorithmic FP64 flop per reactor from the solver's own counters:
-# n_rhs (F_wdot + 6K) + n_setup (2/3 (K+1)^3 + F_jac) + n_newton 2 (K+1)^2, F_jac ~ 1.5 F_wdot
-def ignition_flops(stats, K=53):
-    n = K + 1
-    st = stats.reshape(-1, 8).sum(axis=0).astype(float)
-    rhs, setups, nni = st[1], st[3], st[4]
-    return rhs * (FLOP_PER_STATE + 6 * K) + setups * (2.0 / 3.0 * n ** 3 + 1.5 * FLOP_PER_STATE) + nni * 2.0 * n * n
+# algorithmic FP64 flop per wdot evaluation and mechanism sizes
+MECH = {
+    "gri30": dict(K=53, R=325, flop=38374.0, yaml="gri30.yaml", phase="gri30"),
+    "h2o2": dict(K=10, R=29, flop=3318.0, yaml="h2o2.yaml", phase="ohmech"),
+    "nDodecane_Reitz": dict(K=100, R=553, flop=42252.0, yaml="nDodecane_Reitz.yaml", phase="nDodecane_IG"),
+}
+# dram read+write per gri30 state of the wdot kernel, ncu --set full (profiles/r02_wdot_tile_ncu.txt)
+WDOT_TRAFFIC_BYTES_PER_STATE = 874.8
+
+IGNITION = {
+    # name: mechanism, fuel, O2 per fuel at phi = 1, species names, T0 range, P range [atm], t_end, default reactors
+    "ignition": dict(mech="gri30", fuel="CH4", nO2=2.0, o2="O2", n2="N2", T=(1000.0, 2000.0), P=(1.0, 50.0), tEnd=1e-3,
+                     n=1 << 20, metric="gri30_1ms_ignition_reactors_per_s",
+                     desc="gri30 IdealGasConstPressureMoleReactor advance(1e-3), CH4/air phi 0.5-2, T0 1000-2000 K, P 1-50 atm"),
+    "ndodecane": dict(mech="nDodecane_Reitz", fuel="c12h26", nO2=18.5, o2="o2", n2="n2", T=(700.0, 1400.0), P=(10.0, 50.0),
+                      tEnd=1e-2, n=1 << 18, metric="ndodecane_10ms_ignition_reactors_per_s",
+                      desc="nDodecane_Reitz IdealGasConstPressureMoleReactor advance(1e-2), c12h26/air phi 0.5-2, T0 700-1400 K, P 10-50 atm"),
+    "substep": dict(mech="gri30", fuel="CH4", nO2=2.0, o2="O2", n2="N2", T=(1000.0, 2200.0), P=(1.0, 50.0), tEnd=1e-5,
+                    n=1 << 23, metric="gri30_cfd_substep_cells_per_s",
+                    desc="gri30 operator-split chemistry substep advance(1e-5) from a cold start; cells = CH4/air states "
+                         "taken at 0, 0.25, 0.5, 0.75 and 1 ms along constant-pressure ignition trajectories (cold / igniting / burnt)"),
+}
 
 
 def parse():
@@ -40,11 +68,12 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="wdot", choices=["wdot", "ignition"])
-    ap.add_argument("--states", type=int, default=1 << 22)
-    ap.add_argument("--reactors", type=int, default=1 << 17)
+    ap.add_argument("--workload", default="wdot", choices=["wdot", "ddx", "h2o2", "ignition", "ndodecane", "substep"])
+    ap.add_argument("--states", type=int, default=0, help="states per GPU (wdot, ddx, h2o2); 0 = the config's size")
+    ap.add_argument("--reactors", type=int, default=0, help="reactors / cells IN TOTAL (ignition, ndodecane, substep); 0 = the config's size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-ignition", action="store_true", help="wdot workload: skip the short ignition run reported under 'ignition'")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="wdot workload: skip the ignition and ddx sub-records")
     return ap.parse_args()
 
 
@@ -94,29 +123,37 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-# ------------------------------------------------------------------------------ reference arm
+# ------------------------------------------------------------------------------ the reference
 
 REF_BENCH = os.path.join(ROOT, "oracle", "_ref", "ref_bench")
 REF_DATA = os.path.join(ROOT, "oracle", "_ref", "data")
-IGN_ARGS = ["CH4", "2", "O2", "N2", "1000", "2000", "1", "50", "1e-3"]
 
 
-def run_reference(workload, n, procs, seed=20261104):
-    """The reference's own CPU implementation on `n` states over `procs` worker processes.
-    oracle/_ref/ref_bench (the unmodified reference compiled from its sources) when present
-    ("reference"), else the plain-C oracle port on one core ("port")."""
-    if os.path.exists(REF_BENCH):
-        mode = "wdot" if workload == "wdot" else "ignite"
-        cmd = [REF_BENCH, mode, "gri30.yaml", "gri30", str(n), str(seed), str(procs), REF_DATA]
-        if mode == "ignite":
-            cmd += IGN_ARGS
-        out = subprocess.run(cmd, capture_output=True, text=True, timeout=1800)
-        line = [l for l in out.stdout.splitlines() if l.startswith("{")]
-        if out.returncode == 0 and line:
-            r = json.loads(line[-1])
-            return {"kind": "reference", "cores": procs, "seconds": r["seconds"], "per_second": r["per_second"], "n": n}
-    if workload != "wdot":
+def ref_bench(mode, mech, n, procs, seed=SEED, ign=None, states=None, dump=None, extra=()):
+    """Runs oracle/_ref/ref_bench (the UNMODIFIED reference, one Solution [+ ReactorNet] per worker
+    process). Returns its JSON line as a dict, or None when the binary is missing."""
+    if not os.path.exists(REF_BENCH):
         return None
+    m = MECH[mech]
+    cmd = [REF_BENCH, mode, m["yaml"], m["phase"], str(n), str(seed), str(procs), REF_DATA]
+    if mode == "ignite":
+        c = ign
+        cmd += [c["fuel"], str(c["nO2"]), c["o2"], c["n2"], str(c["T"][0]), str(c["T"][1]), str(c["P"][0]), str(c["P"][1]),
+                repr(c["tEnd"])]
+    if states:
+        cmd += ["--states", states]
+    if dump:
+        cmd += ["--dump", dump]
+    cmd += list(extra)
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)
+    line = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    if out.returncode != 0 or not line:
+        raise RuntimeError("ref_bench failed: %s\n%s" % (" ".join(cmd), out.stderr[-2000:]))
+    return json.loads(line[-1])
+
+
+def oracle_port_wdot(n, seed=SEED):
+    """Fallback CPU baseline when oracle/_ref is absent: the plain-C restatement on one core."""
     import numpy as np
     from oracle.oracle_py import OracleMech
     m = OracleMech(os.path.join(ROOT, "cantera_b200", "data", "gri30.ctbm"))
@@ -128,118 +165,279 @@ def run_reference(workload, n, procs, seed=20261104):
     t0 = time.perf_counter()
     m.rates(T, P, Y, want=("wdot",))
     dt = time.perf_counter() - t0
-    return {"kind": "port", "cores": 1, "seconds": dt, "per_second": n / dt, "n": n}
+    return {"seconds": dt, "per_second": n / dt, "n": n}
 
 
-def metric_of(workload):
-    if workload == "wdot":
-        return "gri30_wdot_evals_per_s", "states/s", "gri30 getNetProductionRates, random (T 800-2500 K, P 1-50 atm, random Y)"
-    return "gri30_1ms_ignition_reactors_per_s", "reactors/s", \
-        "gri30 IdealGasConstPressureMoleReactor advance(1e-3), CH4/air phi 0.5-2, T0 1000-2000 K, P 1-50 atm"
+def cpu_baseline(workload, cores, scale=1):
+    """The reference's CPU path on a bounded sample of the workload (10-30 s of CPU work).
+    Returns the cpu_baseline record."""
+    if workload in IGNITION:
+        c = IGNITION[workload]
+        per_core = {"ignition": 48, "ndodecane": 4, "substep": 2048}[workload]
+        n = per_core * cores * scale
+        r = ref_bench("ignite", c["mech"], n, cores, ign=c)
+        unit = "reactors/s" if workload != "substep" else "cells/s"
+        what = "reactors (one Solution + IdealGasConstPressureMoleReactor + ReactorNet per process, CVODES)"
+    else:
+        mech = "h2o2" if workload == "h2o2" else "gri30"
+        mode = "ddx" if workload == "ddx" else "wdot"
+        per_core = {"wdot": 400000, "h2o2": 2000000, "ddx": 8192}[workload]
+        n = per_core * cores * scale
+        r = ref_bench(mode, mech, n, cores)
+        unit = "states/s"
+        what = "states (one Solution per process)"
+        if r is None and workload == "wdot":
+            r = oracle_port_wdot(200000)
+            return {"value": r["per_second"], "unit": unit, "cores": 1, "kind": "port",
+                    "sample": "%d states through oracle/ctb_oracle.c, %.1f s wall" % (r["n"], r["seconds"])}
+    if r is None:
+        return None
+    return {"value": r["per_second"], "unit": unit, "cores": cores, "kind": "reference",
+            "sample": "%d %s on %d host processes, %.1f s wall" % (r["n"], what, cores, r["seconds"])}
 
 
-def reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return 0
-    metric, unit, desc = metric_of(args.workload)
-    cores = host_cores()
-    # bounded sample: ~3 s (wdot) / ~15 s (ignition) of CPU work per step
-    n = 120000 * cores if args.workload == "wdot" else 24 * cores
-    for _ in range(args.warmup):
-        run_reference(args.workload, max(cores, n // 8), cores)
-    secs, total = 0.0, 0
-    kind = "reference"
-    for _ in range(args.steps):
-        r = run_reference(args.workload, n, cores)
-        if r is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_bench missing for the ignition workload"}))
-            return 0
-        secs += r["seconds"]
-        total += r["n"]
-        kind, cores_used = r["kind"], r["cores"]
-    value = total / secs
-    sample = "%d states per step on %d host processes (one Solution%s per process)" % (
-        n, cores_used, "" if args.workload == "wdot" else " + ReactorNet")
-    line = {
-        "impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "states_per_step": n},
-        "cpu_baseline": {"value": value, "unit": unit, "cores": cores_used, "kind": kind, "sample": sample},
-        "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }
-    print(json.dumps(line))
-    return 0
+# --------------------------------------------------------------------------------- the inputs
 
-
-# ------------------------------------------------------------------------------------ our arm
-
-def make_states(torch, n, K, seed, device):
-    gen = torch.Generator(device=device).manual_seed(seed)
-    T = 800 + 1700 * torch.rand(n, dtype=torch.float64, device=device, generator=gen)
-    P = 101325.0 * (1 + 49 * torch.rand(n, dtype=torch.float64, device=device, generator=gen))
-    Y = torch.rand(n, K, dtype=torch.float64, device=device, generator=gen)
-    Y /= Y.sum(dim=1, keepdim=True)
+def make_states(n, K, seed):
+    """T ~ U(800, 2500) K, P ~ U(1, 50) atm, Y_k = u_k / sum u; numpy, host."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    T = rng.uniform(800.0, 2500.0, n)
+    P = 101325.0 * rng.uniform(1.0, 50.0, n)
+    Y = rng.random((n, K))
+    Y /= Y.sum(axis=1, keepdims=True)
     return T, P, Y
 
 
-def make_ignition_states(torch, n, seed, device):
-    """CH4/air, phi ~ U(0.5, 2), T0 ~ U(1000, 2000) K, P ~ U(1, 50) atm."""
+def make_ignition_states(c, n, seed):
+    """fuel/air, phi ~ U(0.5, 2), T0 and P uniform in the config's ranges."""
     import numpy as np
     from cantera_b200.ctbm import read_arrays
-    tab = read_arrays(os.path.join(ROOT, "cantera_b200", "data", "gri30.ctbm"))
+    mech = c["mech"] if isinstance(c, dict) else "gri30"
+    tab = read_arrays(os.path.join(ROOT, "cantera_b200", "data", mech + ".ctbm"))
     names = tab["species_names"].split("\n")
     W = tab["mol_weights"]
     rng = np.random.default_rng(seed)
-    T = rng.uniform(1000, 2000, n)
-    P = 101325.0 * rng.uniform(1, 50, n)
+    T = rng.uniform(c["T"][0], c["T"][1], n)
+    P = 101325.0 * rng.uniform(c["P"][0], c["P"][1], n)
     phi = rng.uniform(0.5, 2.0, n)
     X = np.zeros((n, len(names)))
-    X[:, names.index("CH4")] = phi
-    X[:, names.index("O2")] = 2.0
-    X[:, names.index("N2")] = 7.52
+    X[:, names.index(c["fuel"])] = phi
+    X[:, names.index(c["o2"])] = c["nO2"]
+    X[:, names.index(c["n2"])] = 3.76 * c["nO2"]
     Y = X * W
     Y /= Y.sum(axis=1, keepdims=True)
     return T, P, Y
 
 
-def ours(args):
+# ------------------------------------------------------------------------------------- parity
+
+def _write_states(path, T, P, Y):
+    from cantera_b200.ctbm import write_arrays
+    import numpy as np
+    write_arrays(path, {"dims": np.array([len(T), Y.shape[1], 0], dtype=np.int32), "T": T, "P": P, "Y": Y.reshape(-1)})
+
+
+def parity_rates(kin, mech, T, P, Y, cores, ddx=False):
+    """First states of the batch through the reference (ref_bench --states --dump) and through the
+    GPU path. wdot: max |dw| / (cdot + ddot) <= 1e-12 (north_star: 1e-12 relative, cancellation-scaled).
+    ddX: max |dJ| / max|J| per state against the reference's default settings, whose falloff term is
+    a finite difference with ~1e-8 noise of its own (MultiRate.h:135-165): <= 1e-6; the analytic
+    agreement at 1e-12 is pinned by tests/test_gpu_kinetics.py."""
+    import numpy as np
+    from cantera_b200.ctbm import read_arrays
+    if not os.path.exists(REF_BENCH):
+        return {"unavailable": "oracle/_ref/ref_bench missing"}
+    n, K = len(T), Y.shape[1]
+    with tempfile.TemporaryDirectory() as d:
+        sp, dp = os.path.join(d, "s.ctbm"), os.path.join(d, "o.ctbm")
+        _write_states(sp, T, P, Y)
+        ref_bench("ddx" if ddx else "wdot", mech, 0, min(cores, 8), states=sp, dump=dp)
+        ref = read_arrays(dp)
+    if ddx:
+        J = kin.net_production_rates_ddX(T, P, Y)
+        Jr = ref["ddX"].reshape(n, K, K)
+        err = float(np.max(np.abs(J - Jr).max(axis=(1, 2)) / np.abs(Jr).max(axis=(1, 2))))
+        return {"n": n, "ddx_max": err, "tol": 1e-6, "ok": bool(err <= 1e-6)}
+    w = kin.net_production_rates(T, P, Y)
+    scale = kin.creation_rates(T, P, Y) + kin.destruction_rates(T, P, Y)
+    err = float(np.max(np.abs(w - ref["wdot"].reshape(n, K)) / np.maximum(scale, 1e-300)))
+    return {"n": n, "wdot_max_scaled": err, "tol": 1e-12, "ok": bool(err <= 1e-12)}
+
+
+def parity_ignition(kin, c, T, P, Y, cores, dT=400.0):
+    """First reactors of the batch through the reference's CVODES ReactorNet at its default
+    tolerances AND at rtol 1e-11 / atol 1e-18 (its converged twin), and through BatchReactorNet.
+    north_star: end states within rtol 1e-6 / atol 1e-12, ignition delay within 0.1 %. Reactors inside
+    their ignition front at t_end (|t_ign - t_end| <= 5 % t_end) are excluded from the state
+    comparison. The reference's own distance from its converged twin is reported beside ours; where it
+    exceeds the tolerance itself (two-stage nDodecane ignition: up to 13x) a state cannot be matched
+    more closely than that, so the pass criterion is |ours - ref| <= tol + 2 |ref - converged|."""
+    import numpy as np
+    from cantera_b200 import BatchReactorNet
+    from cantera_b200.ctbm import read_arrays
+    if not os.path.exists(REF_BENCH):
+        return {"unavailable": "oracle/_ref/ref_bench missing"}
+    n, K = len(T), Y.shape[1]
+    with tempfile.TemporaryDirectory() as d:
+        sp, dp, tp = os.path.join(d, "s.ctbm"), os.path.join(d, "o.ctbm"), os.path.join(d, "t.ctbm")
+        _write_states(sp, T, P, Y)
+        ref_bench("ignite", c["mech"], 0, cores, ign=c, states=sp, dump=dp, extra=["--tign", str(dT)])
+        ref_bench("ignite", c["mech"], 0, cores, ign=c, states=sp, dump=tp, extra=["--tign", str(dT), "--rtol", "1e-11", "--atol", "1e-18"])
+        ref, conv = read_arrays(dp), read_arrays(tp)
+    net = BatchReactorNet(kin, n)
+    net.set_state(T, P, Y)
+    net.set_ignition_monitor(dT)
+    net.advance(c["tEnd"])
+    Te, Ye = net.get_state()
+    tign, status = net.ignition_delay(), net.status()
+    net.close()
+    Tr, Yr, tr = ref["Tend"], ref["Yend"].reshape(n, K), ref["tign"]
+    Yc = conv["Yend"].reshape(n, K)
+    ign = np.isfinite(tr)
+    front = ign & (np.abs(tr - c["tEnd"]) <= 0.05 * c["tEnd"])
+    ok = ~front
+    tol = 1e-6 * np.abs(Yr) + 1e-12
+    refself = np.abs(Yr - Yc)
+    out = {
+        "n": n, "failed": int((status != 0).sum()), "ignited": int(ign.sum()), "in_front_excluded": int(front.sum()),
+        "T_end_max_rel": float(np.max(np.abs(Te[ok] - Tr[ok]) / Tr[ok])),
+        "Y_end_worst_over_tol": float(np.max((np.abs(Ye - Yr) / tol)[ok])),
+        "Y_end_ref_vs_converged_over_tol": float(np.max((refself / tol)[ok])),
+        "Y_end_ours_vs_converged_over_tol": float(np.max((np.abs(Ye - Yc) / tol)[ok])),
+        "tign_max_rel": float(np.max(np.abs(tign[ign] - tr[ign]) / tr[ign])) if ign.any() else 0.0,
+        "tign_same_set": bool(np.array_equal(np.isfinite(tign), ign)),
+    }
+    out["ok"] = bool(out["failed"] == 0 and out["tign_max_rel"] <= 1e-3 and out["tign_same_set"]
+                     and np.all((np.abs(Ye - Yr) <= tol + 2.0 * refself)[ok])
+                     and np.all(np.abs(Te[ok] - Tr[ok]) <= 1e-6 * Tr[ok] + 2.0 * np.abs(Tr[ok] - conv["Tend"][ok])))
+    return out
+
+
+# ------------------------------------------------------------------------------------ our arm
+
+class Ctx:
+    pass
+
+
+def setup():
     import torch
     import torch.distributed as dist
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
+    x = Ctx()
+    x.torch, x.dist = torch, dist
+    x.rank = int(os.environ.get("RANK", "0"))
+    x.local = int(os.environ.get("LOCAL_RANK", "0"))
+    x.world = int(os.environ.get("WORLD_SIZE", "1"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; this engine has no CPU path")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    from cantera_b200 import BatchedGasKinetics, BatchReactorNet
-    kin = BatchedGasKinetics("gri30", device=local)
-    kin.use_torch_stream()
-    K = kin.n_species
-    metric, unit, desc = metric_of(args.workload)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    launches = 0
-    # FP64 roofline denominator: measured live by the library's DFMA micro-benchmark (MEASURED_PEAKS.json
-    # carries no FP64 figure); the nominal number is kept beside it
+    torch.cuda.set_device(x.local)
+    x.dev = torch.device("cuda", x.local)
+    if x.world > 1:
+        dist.init_process_group("nccl", device_id=x.dev)
     from cantera_b200 import clib
-    fp64_peak = float(clib.lib().ctb_fp64PeakTflops(local))
-    if not fp64_peak > 0:
-        fp64_peak = FP64_PEAK_TFLOPS_NOMINAL
-    ign_stats = {}
-    if args.workload == "wdot":
-        n = args.states
-        T, P, Y = make_states(torch, n, K, 20261104 + rank, dev)
-        out = torch.empty(n, K, dtype=torch.float64, device=dev)
-        hT, hP, hY = T.cpu().pin_memory(), P.cpu().pin_memory(), Y.cpu().pin_memory()
+    x.fp64_peak = float(clib.lib().ctb_fp64PeakTflops(x.local))
+    if not x.fp64_peak > 0:
+        x.fp64_peak = FP64_PEAK_TFLOPS_NOMINAL
+    x.peaks = measured_peaks()
+    x.cores = host_cores()
+    return x
+
+
+def barrier(x):
+    if x.world > 1:
+        x.dist.barrier()
+    x.torch.cuda.synchronize()
+
+
+def reduce_max(x, vals):
+    if x.world == 1:
+        return list(vals)
+    t = x.torch.tensor(list(vals), dtype=x.torch.float64, device=x.dev)
+    x.dist.all_reduce(t, op=x.dist.ReduceOp.MAX)
+    return t.tolist()
+
+
+def reduce_sum(x, vals):
+    if x.world == 1:
+        return list(vals)
+    t = x.torch.tensor(list(vals), dtype=x.torch.float64, device=x.dev)
+    x.dist.all_reduce(t, op=x.dist.ReduceOp.SUM)
+    return t.tolist()
+
+
+def timed_steps(x, step, steps, warmup):
+    """W untimed warm-up steps, then K steps bracketed by barrier + synchronize; CUDA events on the
+    launching stream. Returns (total ms = max over ranks, mean per-step kernel ms of this rank)."""
+    torch = x.torch
+    for _ in range(warmup):
+        step()
+    barrier(x)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    per = []
+    ev0.record()
+    for _ in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step()
+        b.record()
+        per.append((a, b))
+    ev1.record()
+    barrier(x)
+    ms = ev0.elapsed_time(ev1)
+    kernel_ms = sum(a.elapsed_time(b) for a, b in per) / steps
+    return reduce_max(x, [ms])[0], kernel_ms
+
+
+def timed_e2e(x, step_e2e, steps):
+    """The same step through the C ABI with pinned HOST buffers, copies inside the timed region
+    (wall clock around synchronised calls; max over ranks)."""
+    step_e2e()
+    barrier(x)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step_e2e()
+    x.torch.cuda.synchronize()
+    ms = 1e3 * (time.perf_counter() - t0)
+    return reduce_max(x, [ms])[0]
+
+
+def rates_workload(x, args, workload):
+    """wdot / h2o2 / ddx: weak scaling, every rank its own batch (seed + rank)."""
+    import numpy as np
+    torch = x.torch
+    from cantera_b200 import BatchedGasKinetics
+    mech = "h2o2" if workload == "h2o2" else "gri30"
+    m = MECH[mech]
+    K = m["K"]
+    kin = BatchedGasKinetics(mech, device=x.local)
+    kin.use_torch_stream()
+    n = args.states or {"wdot": 1 << 22, "ddx": 1 << 22, "h2o2": 1 << 20}[workload]
+    hT, hP, hY = make_states(n, K, SEED + {"wdot": 1, "ddx": 1, "h2o2": 0}[workload] + 1000 * x.rank)
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    hT, hP, hY = pin(hT), pin(hP), pin(hY)
+    T, P, Y = hT.to(x.dev), hP.to(x.dev), hY.to(x.dev)
+    steps, warmup = args.steps, args.warmup
+    if workload == "ddx":
+        chunk = min(n, 1 << 19)
+        out = torch.empty(chunk, K, K, dtype=torch.float64, device=x.dev)  # 11.8 GB, re-used by every chunk
+        hchunk = min(n, 1 << 16)
+        hout = torch.empty(hchunk, K, K, dtype=torch.float64).pin_memory()
+
+        def step():
+            for b in range(0, n, chunk):
+                e = min(n, b + chunk)
+                kin.net_production_rates_ddX(T[b:e], P[b:e], Y[b:e], out=out[: e - b])
+
+        def step_e2e():
+            kin.net_production_rates_ddX(hT.numpy()[:hchunk], hP.numpy()[:hchunk], hY.numpy()[:hchunk], out=hout.numpy())
+
+        launches_per_step = (n + chunk - 1) // chunk
+        e2e_units, h2d, d2h = hchunk, 8 * hchunk * (K + 2), 8 * hchunk * K * K
+        metric = "gri30_ddx_jacobians_per_s"
+        desc = "gri30 netProductionRates_ddX (dense K x K per state), random (T 800-2500 K, P 1-50 atm, random Y)"
+        l2 = "output 22.5 KB per state, %d-state chunks (11.8 GB) >> 126 MB L2" % chunk
+    else:
+        out = torch.empty(n, K, dtype=torch.float64, device=x.dev)
         hout = torch.empty(n, K, dtype=torch.float64).pin_memory()
 
         def step():
@@ -248,139 +446,272 @@ def ours(args):
         def step_e2e():
             kin.net_production_rates(hT.numpy(), hP.numpy(), hY.numpy(), out=hout.numpy())
 
-        units, h2d, d2h, launches_per_step = n, 8 * n * (K + 2), 8 * n * K, 1
-        l2_note = "inputs+outputs 3.6 GB per step >> 126 MB L2"
-    else:
-        n = args.reactors
-        Tn, Pn, Yn = make_ignition_states(torch, n, 20261104 + rank, dev)
-        T, P, Y = (torch.from_numpy(a).to(dev) for a in (Tn, Pn, Yn))
-        net = BatchReactorNet(kin, n)
-        state = {}
-
-        def step():
-            net.set_state(T, P, Y)
-            net.advance(1e-3)
-            state["out"] = net.get_state(device_like=T)
-            ign_stats["stats"] = net.solver_stats()
-
-        def step_e2e():
-            net.set_state(Tn, Pn, Yn)
-            net.advance(1e-3)
-            state["host"] = net.get_state()
-
-        units, h2d, d2h, launches_per_step = n, 8 * n * (K + 2), 8 * n * (K + 1), 0
-        l2_note = "reactor state and integrator memory %d MB per step" % (n * 8 * 12 * (K + 1) >> 20)
-
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
+        launches_per_step = 1
+        e2e_units, h2d, d2h = n, 8 * n * (K + 2), 8 * n * K
+        metric = "%s_wdot_evals_per_s" % mech
+        desc = "%s getNetProductionRates, random (T 800-2500 K, P 1-50 atm, random Y)" % mech
+        l2 = "inputs+outputs %.2f GB per step > 126 MB L2" % ((h2d + d2h) / 1e9)
+    sampler = ClockSampler(x.local)
     sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    per_step = []
-    ev0.record()
-    for _ in range(args.steps):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        step()
-        b.record()
-        per_step.append((a, b))
-        launches += launches_per_step
-        if args.workload == "ignition":
-            launches += 3 + 4 * net.last_rounds()  # init, contents + (memset-free) control, rhs, setup, lu per round
-    ev1.record()
-    barrier()
+    ms, kernel_ms = timed_steps(x, step, steps, warmup)
     sampler.stop_flag = True
     sampler.join()
-    ms = ev0.elapsed_time(ev1)
-    kernel_ms = sum(a.elapsed_time(b) for a, b in per_step) / args.steps
-    # end to end through the C ABI with HOST buffers (pinned), copies inside the timed region
-    e2e_steps = max(1, min(args.steps, 3))
-    step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        step_e2e()
-    torch.cuda.synchronize()
-    e2e_ms = 1e3 * (time.perf_counter() - t0)
-    if world > 1:
-        t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms = t.tolist()
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
-    value = units * world * args.steps / (ms * 1e-3)
-    e2e_value = units * world * e2e_steps / (e2e_ms * 1e-3)
-    peaks = measured_peaks()
-    line = {
-        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "states_per_gpu": units, "mechanism": "gri30 (53 species, 325 reactions)",
-                   "l2": l2_note},
+    e2e_steps = max(1, min(steps, 3))
+    e2e_ms = timed_e2e(x, step_e2e, e2e_steps)
+    rec = {
+        "metric": metric, "value": n * x.world * steps / (ms * 1e-3), "unit": "states/s", "n_gpus": x.world,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "states_per_gpu": n, "mechanism": "%s (%d species, %d reactions)" % (mech, K, m["R"]), "l2": l2},
         "clocks": sampler.result(),
-        "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps},
-        "gpu_launches": launches,
+        "e2e": {"value": e2e_units * x.world * e2e_steps / (e2e_ms * 1e-3), "unit": "states/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "states_per_step": e2e_units},
+        "gpu_launches": launches_per_step * steps,
     }
-    if args.workload == "wdot":
-        # dominant kernel = ratesKernel (the only launch of a step). FP64-pipe bound:
-        # the contract's "tensor" slot carries the compute roofline; the HBM view is given alongside.
-        tflops = FLOP_PER_STATE * units / (kernel_ms * 1e-3) / 1e12
-        gbs = BYTES_PER_STATE * units / (kernel_ms * 1e-3) / 1e9
-        line["roofline"] = {
-            "bound": "tensor", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s",
-            "frac": tflops / fp64_peak, "traffic": WDOT_TRAFFIC_BYTES_PER_STATE * units,
-            "note": "FP64 DFMA pipe (no tensor cores on this path; the contract's 'tensor' slot carries the compute "
-                    "roofline). peak = measured live by ctb_fp64PeakTflops (register-resident DFMA micro-benchmark; "
-                    "nominal 148 SM x 64 DFMA/clk x 1.965 GHz = %.1f); algorithmic flop/state = 38374 (SURVEY.md 8(d)); "
-                    "traffic = dram bytes/state of the ncu capture in profiles/ x states" % FP64_PEAK_TFLOPS_NOMINAL,
-            "hbm": {"achieved_gbs": gbs, "peak_gbs": peaks.get("hbm_gbs"), "frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
-                    "bytes_per_state": BYTES_PER_STATE},
-            "kernel_ms": kernel_ms,
-        }
-    if args.workload == "ignition" and "stats" in ign_stats:
-        import numpy as np
-        st = np.asarray(ign_stats["stats"]).reshape(-1, 8)
-        fl = ignition_flops(st)
-        tflops = fl / (kernel_ms * 1e-3) / 1e12
-        tot = st.sum(axis=0)
-        line["roofline"] = {
-            "bound": "tensor", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
-            "traffic": None,
-            "note": "FP64 DFMA pipe; algorithmic flop from the solver's counters: n_rhs (F_wdot + 6K) + n_setup "
-                    "(2/3 (K+1)^3 + 1.5 F_wdot) + n_newton 2 (K+1)^2; peak measured live by ctb_fp64PeakTflops",
-            "per_reactor": {"steps": tot[0] / n, "rhs": tot[1] / n, "setups": tot[3] / n, "newton_iters": tot[4] / n},
-            "rounds": net.last_rounds(), "kernel_ms": kernel_ms,
-        }
-    if args.workload == "wdot" and not args.no_ignition and world == 1:
-        # the second half of BASELINE.json's metric, on a bounded batch (one timed advance after one warm-up)
-        n_ign = 131072
-        Tn, Pn, Yn = make_ignition_states(torch, n_ign, 20261104, dev)
-        Ti, Pi, Yi = (torch.from_numpy(a).to(dev) for a in (Tn, Pn, Yn))
-        net = BatchReactorNet(kin, n_ign)
-        for rep_i in range(2):
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            net.set_state(Ti, Pi, Yi)
-            net.advance(1e-3)
-            torch.cuda.synchronize()
-            ign_s = time.perf_counter() - t0
-        line["ignition"] = {"metric": "gri30_1ms_ignition_reactors_per_s", "value": n_ign / ign_s, "unit": "reactors/s",
-                            "reactors": n_ign, "seconds": ign_s, "failed": int((net.status() != 0).sum())}
-        net.close()
-    if not args.no_cpu_baseline:
-        cores = host_cores()
-        nref = 400000 * cores if args.workload == "wdot" else 24 * cores
-        r = run_reference(args.workload, nref, cores)
-        if r:
-            line["cpu_baseline"] = {"value": r["per_second"], "unit": unit, "cores": r["cores"], "kind": r["kind"],
-                                    "sample": "%d states, %.1f s wall" % (r["n"], r["seconds"])}
-    print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    hbm = x.peaks.get("hbm_gbs")
+    if workload == "ddx":
+        bytes_per = 8 * (K + 2) + 8 * K * K
+        gbs = bytes_per * n / (kernel_ms * 1e-3) / 1e9
+        peak = hbm or 6541.5
+        rec["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                           "note": "jacKernel writes the dense K x K Jacobian: algorithmic bytes = 8 (K + 2) + 8 K^2 = %d per state "
+                                   "(SURVEY.md 8(d)); peak = MEASURED_PEAKS.json hbm_gbs%s" % (bytes_per, "" if hbm else " (absent: fallback 6541.5)"),
+                           "kernel_ms": kernel_ms}
+    else:
+        tflops = m["flop"] * n / (kernel_ms * 1e-3) / 1e12
+        bytes_per = 8 * (K + 2) + 8 * K
+        gbs = bytes_per * n / (kernel_ms * 1e-3) / 1e9
+        rec["roofline"] = {
+            "bound": "tensor", "achieved": tflops, "peak": x.fp64_peak, "unit": "TFLOP/s", "frac": tflops / x.fp64_peak,
+            "traffic": WDOT_TRAFFIC_BYTES_PER_STATE * n if mech == "gri30" else None,
+            "note": "FP64 DFMA pipe (no tensor cores on this path; the contract's 'tensor' slot carries the compute roofline). "
+                    "peak = measured live by ctb_fp64PeakTflops (register-resident DFMA micro-benchmark; nominal 148 SM x 64 "
+                    "DFMA/clk x 2 x 1.965 GHz = %.1f); algorithmic flop/state = %d (SURVEY.md 8(d)); traffic = dram bytes/state "
+                    "of the ncu capture in profiles/ x states" % (FP64_PEAK_TFLOPS_NOMINAL, m["flop"]),
+            "hbm": {"achieved_gbs": gbs, "peak_gbs": hbm, "frac": gbs / hbm if hbm else None, "bytes_per_state": bytes_per},
+            "kernel_ms": kernel_ms}
+    if x.rank == 0 and not args.no_parity:
+        npar = 256 if workload == "ddx" else 4096
+        rec["parity"] = parity_rates(kin, mech, hT.numpy()[:npar], hP.numpy()[:npar], hY.numpy()[:npar], x.cores, ddx=workload == "ddx")
+    if x.rank == 0 and not args.no_cpu_baseline:
+        rec["cpu_baseline"] = cpu_baseline(workload, x.cores)
+    del out, T, P, Y
+    kin.close()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def ignition_flops(stats, mech):
+    """Algorithmic FP64 flop of an advance from the solver's own counters:
+    n_rhs (F_wdot + 6K) + n_setup (2/3 (K+1)^3 + 1.5 F_wdot) + n_newton 2 (K+1)^2."""
+    m = MECH[mech]
+    K, n = m["K"], m["K"] + 1
+    st = stats.reshape(-1, 8).sum(axis=0).astype(float)
+    rhs, setups, nni = st[1], st[3], st[4]
+    return rhs * (m["flop"] + 6 * K) + setups * (2.0 / 3.0 * n ** 3 + 1.5 * m["flop"]) + nni * 2.0 * n * n
+
+
+def substep_states(x, kin, c, n_base, seed):
+    """Config 5 cells: CH4/air states taken at 0, 0.25, 0.5, 0.75, 1 ms along constant-pressure ignition
+    trajectories (cold / igniting / burnt mix). Returns numpy (T, P, Y) of 5 n_base cells."""
+    import numpy as np
+    from cantera_b200 import BatchReactorNet
+    T0, P0, Y0 = make_ignition_states(c, n_base, seed)
+    net = BatchReactorNet(kin, n_base)
+    net.set_state(T0, P0, Y0)
+    Ts, Ys = [T0], [Y0]
+    for t in (0.25e-3, 0.5e-3, 0.75e-3, 1e-3):
+        net.advance(t)
+        Te, Ye = net.get_state()
+        Ts.append(Te)
+        Ys.append(Ye)
+    net.close()
+    return np.concatenate(Ts), np.tile(P0, 5), np.concatenate(Ys)
+
+
+def reactor_workload(x, args, workload, n_total=None, steps=None, warmup=None):
+    """ignition / ndodecane / substep: ONE seeded batch of n_total reactors, every rank integrates its
+    share of a seeded permutation (cantera_b200.sharding.permuted_indices): strong scaling."""
+    import numpy as np
+    torch = x.torch
+    from cantera_b200 import BatchedGasKinetics, BatchReactorNet
+    from cantera_b200.sharding import permuted_indices
+    c = IGNITION[workload]
+    mech = c["mech"]
+    m = MECH[mech]
+    K = m["K"]
+    kin = BatchedGasKinetics(mech, device=x.local)
+    kin.use_torch_stream()
+    n_total = n_total or args.reactors or c["n"]
+    steps = steps if steps is not None else args.steps
+    warmup = warmup if warmup is not None else args.warmup
+    seed = SEED + {"ignition": 3, "ndodecane": 4, "substep": 5}[workload]
+    mine = permuted_indices(n_total, x.rank, x.world, seed)
+    if workload == "substep":
+        base = min(n_total // 5, 1 << 15)
+        Tb, Pb, Yb = substep_states(x, kin, c, base, seed)
+        idx = mine % len(Tb)
+        Tn, Pn, Yn = Tb[idx], Pb[idx], Yb[idx]
+        par_T, par_P, par_Y = Tb[np.arange(512) * (len(Tb) // 512)], Pb[np.arange(512) * (len(Tb) // 512)], Yb[np.arange(512) * (len(Tb) // 512)]
+    else:
+        Tg, Pg, Yg = make_ignition_states(c, n_total, seed)  # the one global batch, identical on every rank
+        Tn, Pn, Yn = Tg[mine], Pg[mine], Yg[mine]
+        npar = 512 if mech == "gri30" else 128
+        par_T, par_P, par_Y = Tg[:npar], Pg[:npar], Yg[:npar]
+        del Tg, Pg, Yg
+    n = len(mine)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    hT, hP, hY = pin(Tn), pin(Pn), pin(Yn)
+    T, P, Y = hT.to(x.dev), hP.to(x.dev), hY.to(x.dev)
+    net = BatchReactorNet(kin, n)
+    keep = {}
+
+    def step():
+        net.set_state(T, P, Y)
+        net.advance(c["tEnd"])
+        keep["out"] = net.get_state(device_like=T)
+
+    def step_e2e():
+        net.set_state(hT.numpy(), hP.numpy(), hY.numpy())
+        net.advance(c["tEnd"])
+        keep["host"] = net.get_state()
+
+    sampler = ClockSampler(x.local)
+    sampler.start()
+    e2e_steps = 1
+    if steps == 1 and warmup == 0:
+        # single-shot mode (the sub-record of the default line): ONE advance through pinned host buffers
+        # is both numbers: e2e = the whole call, value = the same run's device time between the copies
+        barrier(x)
+        t0 = time.perf_counter()
+        net.set_state(hT.numpy(), hP.numpy(), hY.numpy())
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        net.advance(c["tEnd"])
+        keep["out"] = net.get_state(device_like=T)
+        b.record()
+        keep["host"] = net.get_state()
+        torch.cuda.synchronize()
+        e2e_ms = 1e3 * (time.perf_counter() - t0)
+        kernel_ms = a.elapsed_time(b)
+        ms, e2e_ms = reduce_max(x, [kernel_ms, e2e_ms])
+    else:
+        ms, kernel_ms = timed_steps(x, step, steps, warmup)
+        e2e_ms = timed_e2e(x, step_e2e, e2e_steps)
+    sampler.stop_flag = True
+    sampler.join()
+    stats = net.solver_stats()
+    rounds = net.last_rounds()
+    failed = int((net.status() != 0).sum())
+    flop = ignition_flops(stats, mech)
+    tot = stats.sum(axis=0).astype(float)
+    flop_all, failed_all, n_all = reduce_sum(x, [flop, failed, n])
+    unit = "cells/s" if workload == "substep" else "reactors/s"
+    rec = {
+        "metric": c["metric"], "value": n_total * steps / (ms * 1e-3), "unit": unit, "n_gpus": x.world, "steps": steps,
+        "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": c["desc"], "reactors_total": n_total, "reactors_this_rank": n,
+                   "mechanism": "%s (%d species, %d reactions)" % (mech, K, m["R"]),
+                   "sharding": "shares of one seeded permutation of the global batch (cantera_b200.sharding.permuted_indices)",
+                   "l2": "reactor state and integrator memory %d MB per GPU >> 126 MB L2" % (n * 8 * 12 * (K + 1) >> 20)},
+        "clocks": sampler.result(),
+        "e2e": {"value": n_total * e2e_steps / (e2e_ms * 1e-3), "unit": unit, "h2d_bytes_per_step": 8 * n * (K + 2),
+                "d2h_bytes_per_step": 8 * n * (K + 1), "steps": e2e_steps},
+        "gpu_launches": steps * (3 + 4 * rounds),
+        "failed_reactors": int(failed_all),
+    }
+    tflops = flop_all / x.world / (kernel_ms * 1e-3) / 1e12  # per GPU (this rank's kernel time, all ranks' mean flop)
+    rec["roofline"] = {
+        "bound": "tensor", "achieved": tflops, "peak": x.fp64_peak, "unit": "TFLOP/s", "frac": tflops / x.fp64_peak, "traffic": None,
+        "note": "FP64 DFMA pipe, per GPU; algorithmic flop from the solver's counters: n_rhs (F_wdot + 6K) + n_setup "
+                "(2/3 (K+1)^3 + 1.5 F_wdot) + n_newton 2 (K+1)^2; peak measured live by ctb_fp64PeakTflops",
+        "per_reactor": {"steps": tot[0] / n, "rhs": tot[1] / n, "setups": tot[3] / n, "newton_iters": tot[4] / n},
+        "rounds": rounds, "kernel_ms": kernel_ms}
+    if x.rank == 0 and not args.no_parity:
+        rec["parity"] = parity_ignition(kin, c, par_T, par_P, par_Y, x.cores)
+    if x.rank == 0 and not args.no_cpu_baseline:
+        rec["cpu_baseline"] = cpu_baseline(workload, x.cores)
+    net.close()
+    kin.close()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def ours(args):
+    x = setup()
+    if args.workload in IGNITION:
+        rec = reactor_workload(x, args, args.workload)
+    else:
+        rec = rates_workload(x, args, args.workload)
+        if args.workload == "wdot" and not args.no_sub:
+            # the other half of BASELINE.json's metric, and the HBM-bound Jacobian, on the same line
+            rec["ignition"] = reactor_workload(x, args, "ignition", steps=1, warmup=0)
+            sub = argparse.Namespace(**vars(args))
+            sub.steps, sub.warmup = 3, 1
+            rec["ddx"] = rates_workload(x, sub, "ddx")
+    rc = 0
+    if x.rank == 0:
+        bad = [k for k, r in [("", rec)] + [(k, rec[k]) for k in ("ignition", "ddx") if k in rec]
+               if isinstance(r.get("parity"), dict) and r["parity"].get("ok") is False]
+        if rec.get("failed_reactors") or rec.get("ignition", {}).get("failed_reactors"):
+            bad.append("failed_reactors")
+        if bad:
+            rec["parity_failed"] = bad
+            rc = 3
+        print(json.dumps(rec))
+    if x.world > 1:
+        x.dist.destroy_process_group()
+    return rc
+
+
+# ------------------------------------------------------------------------------ reference arm
+
+def reference_record(workload, args, cores, steps, warmup):
+    """The unmodified reference's CPU implementation of the workload on all host cores, each step a
+    bounded sample of the workload."""
+    for _ in range(warmup):
+        cpu_baseline(workload, cores)
+    secs, total, last = 0.0, 0.0, None
+    for _ in range(steps):
+        r = cpu_baseline(workload, cores)
+        if r is None:
+            return None
+        n = int(r["sample"].split()[0])
+        secs += n / r["value"]
+        total += n
+        last = r
+    value = total / secs
+    unit = last["unit"]
+    if workload in IGNITION:
+        metric, desc = IGNITION[workload]["metric"], IGNITION[workload]["desc"]
+    else:
+        mech = "h2o2" if workload == "h2o2" else "gri30"
+        metric = "gri30_ddx_jacobians_per_s" if workload == "ddx" else "%s_wdot_evals_per_s" % mech
+        desc = ("gri30 netProductionRates_ddX (dense K x K per state)" if workload == "ddx" else "%s getNetProductionRates" % mech) \
+            + ", random (T 800-2500 K, P 1-50 atm, random Y)"
+    return {
+        "impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+        "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "strong" if workload in IGNITION else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "units_per_step": int(total / steps)},
+        "cpu_baseline": {"value": value, "unit": unit, "cores": last["cores"], "kind": last["kind"], "sample": last["sample"]},
+        "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    cores = host_cores()
+    rec = reference_record(args.workload, args, cores, args.steps, args.warmup)
+    if rec is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_bench missing (the reference is built by oracle/ref_build/build_ref.sh)"}))
+        return 0
+    if args.workload == "wdot" and not args.no_sub:
+        rec["ignition"] = reference_record("ignition", args, cores, 1, 0)
+        rec["ddx"] = reference_record("ddx", args, cores, 1, 0)
+    print(json.dumps(rec))
     return 0
 
 

@@ -5,8 +5,9 @@ Python names as in interfaces/cython/cantera/kinetics.pyx: ``net_production_rate
 ``forward_rates_of_progress``, ``net_production_rates_ddX`` ...), ``BatchReactorNet`` follows
 ``ReactorNet`` + ``IdealGasConstPressureMoleReactor`` (include/cantera/zeroD/ReactorNet.h:57,159).
 Every call goes through the C ABI (include/ctb_clib.h). Arrays are either numpy (host memory,
-staged by the library) or torch CUDA tensors (device memory, no copies; the call is queued on
-torch's current stream).
+staged by the library) or torch CUDA tensors (device memory, no copies; every such call first points
+the handle at torch's current stream, so it is ordered against the producers and consumers of the
+tensors).
 """
 import os
 
@@ -105,9 +106,17 @@ class BatchedGasKinetics:
         return self._h
 
     def use_torch_stream(self):
-        """Queue subsequent device-memory calls on torch's current CUDA stream."""
+        """Queue subsequent device-memory calls on torch's current CUDA stream. (Every call that is
+        handed torch tensors does this itself, see _on_torch_stream; kept for explicit use.)"""
         import torch
         clib.check(self._lib.ctb_kin_setStream(self._h, torch.cuda.current_stream().cuda_stream))
+
+    def _on_torch_stream(self, batch):
+        """Device-memory (torch) arguments: the kernels are queued on torch's CURRENT stream, so they are
+        ordered after the kernels that produced the inputs and before whatever consumes the outputs,
+        and the caching allocator's stream bookkeeping stays valid."""
+        if batch.space == clib.DEVICE:
+            clib.check(self._lib.ctb_kin_setStream(self._h, batch.torch.cuda.current_stream().cuda_stream))
 
     def synchronize(self):
         clib.check(self._lib.ctb_kin_synchronize(self._h))
@@ -126,6 +135,7 @@ class BatchedGasKinetics:
     # ---- getters
     def _species(self, fn, T, P, Y, out=None):
         b = _Batch(T, P, Y, self.n_species)
+        self._on_torch_stream(b)
         if out is None:
             out = b.empty(b.N, self.n_species)
         if b.N:
@@ -134,6 +144,7 @@ class BatchedGasKinetics:
 
     def _reaction(self, fn, T, P, Y, out=None):
         b = _Batch(T, P, Y, self.n_species)
+        self._on_torch_stream(b)
         if out is None:
             out = b.empty(b.N, self.n_reactions)
         if b.N:
@@ -167,6 +178,7 @@ class BatchedGasKinetics:
 
     def _jac(self, fn, T, P, Y, out):
         b = _Batch(T, P, Y, self.n_species)
+        self._on_torch_stream(b)
         K = self.n_species
         if out is None:
             out = b.empty(b.N, K, K)
@@ -209,6 +221,7 @@ class BatchReactorNet:
         b = _Batch(T, P, Y, self.kinetics.n_species)
         if b.N != self.n_reactors:
             raise clib.CtbError(f"expected {self.n_reactors} states, got {b.N}")
+        self.kinetics._on_torch_stream(b)
         clib.check(self._lib.ctb_reactornet_setState(self._h, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, b.space))
 
     @property
@@ -260,6 +273,7 @@ class BatchReactorNet:
             T = torch.empty(self.n_reactors, dtype=torch.float64, device=device_like.device)
             Y = torch.empty(self.n_reactors, K, dtype=torch.float64, device=device_like.device)
             space = clib.DEVICE
+            clib.check(self._lib.ctb_kin_setStream(self.kinetics.handle, torch.cuda.current_stream().cuda_stream))
         else:
             T = np.empty(self.n_reactors)
             Y = np.empty((self.n_reactors, K))

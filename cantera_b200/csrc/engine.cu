@@ -56,6 +56,7 @@ BatchedGasKinetics::BatchedGasKinetics(const ctb_mech_tables& tables, int device
         throw CtbError("BatchedGasKinetics", ex.what());
     }
     m_dev.view = m_packed.v;
+    m_dev.tile = m_packed.tv;
     m_dev.device = device;
     m_dev.numSMs = prop.multiProcessorCount;
     cudaCheck(cudaDeviceGetAttribute(&m_dev.smemOptIn, cudaDevAttrMaxSharedMemoryPerBlockOptin, device),
@@ -83,11 +84,15 @@ BatchedGasKinetics::~BatchedGasKinetics()
 
 void BatchedGasKinetics::uploadMultipliers()
 {
-    const int R = nReactions();
-    double* dst = reinterpret_cast<double*>(m_packed.blob.data() + m_packed.v.o_mult);
-    for (int e = 0; e < R; e++) dst[e] = m_tables.multiplier[m_packed.perm[e]];
+    // the multipliers are folded into several tables (o_mult, the tile region's A and auxMult):
+    // repack (same layout, same size) and upload the whole image; setMultiplier is a rare call
+    PackedMech again = packMechanism(m_tables.view());
+    if (again.blob.size() != m_packed.blob.size()) throw CtbError("BatchedGasKinetics::setMultiplier", "image size changed");
+    m_packed = std::move(again);
+    m_dev.view = m_packed.v;
+    m_dev.tile = m_packed.tv;
     cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
-    cudaCheck(cudaMemcpy(m_dev.dBlob + m_packed.v.o_mult, dst, sizeof(double) * R, cudaMemcpyHostToDevice),
+    cudaCheck(cudaMemcpy(m_dev.dBlob, m_packed.blob.data(), m_packed.blob.size(), cudaMemcpyHostToDevice),
               "cudaMemcpy(multipliers)");
 }
 

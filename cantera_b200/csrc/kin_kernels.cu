@@ -11,6 +11,7 @@
 #define CTB_EXP_LIB
 #include "kin_kernels.h"
 #include "rates_thread.cuh"
+#include "rates_tile.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -124,6 +125,129 @@ __global__ void __launch_bounds__(512) ratesKernel(const MechView v, const unsig
     }
 }
 
+
+// ------------------------------------------------------------------------------- rates, tiles
+
+//! setState_TPY + updateROP + getNetProductionRates for tiles of 16 states (rates_tile.cuh): W warps
+//! per tile, several tiles per CTA, persistent grid. Shared memory:
+//!   [tile tables (TMA bulk copy)] [mbarrier] [per tile: c/wdot rows, u rows, v rows, q rows, scratch]
+template <int W, int MAXT, int ILP>
+__global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
+                                                        const RatesArgs a, const int tileDoubles, const int tableBytes)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + tableBytes);
+    tmaStage(smem, gblob + tv.begin, tv.bytes, bar);
+    constexpr int TT = W * 32, NL = 2 * W;
+    const int ti = threadIdx.x / TT, tid = threadIdx.x % TT;
+    const int tilesPerCta = blockDim.x / TT;
+    const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
+    const int K = tv.K, R = tv.R;
+    double* c = reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles;
+    double* u = c + K * CTB_LDC;
+    double* v = u + K * CTB_LDC;
+    double* q = v + K * CTB_LDC;
+    double* red = q; // [2][NL][16] scratch of the normalisation sums: dead before the q rows are written
+    Tile t;
+    t.tp = smem;
+    t.cS = c + s; t.uS = u + s; t.vS = v + s; t.qS = q + s;
+    const unsigned char* spTab = smem + tv.o_sp;
+    if (tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
+    volatile int* safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
+    if (tid == 0) *safeFlag = 0;
+    const int barId = 1 + ti;
+    const long long nTiles = (a.N + CTB_TS - 1) / CTB_TS;
+    const bool needLogP = tv.hasPdep != 0;
+    for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
+        const long long n0 = tile * CTB_TS;
+        const int nvalid = (int) min((long long) CTB_TS, a.N - n0);
+        // ---- coalesced transposed load of the tile's mass fractions into the c rows
+        for (int i = tid; i < CTB_TS * K; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicK);
+            const int k = i - si * K;
+            const int sn = min(si, nvalid - 1);
+            c[k * CTB_LDC + si] = a.Y[(n0 + sn) * a.ldY + k];
+        }
+        const long long n = n0 + min(s, nvalid - 1);
+        TileScalars sc;
+        sc.T = a.T[n];
+        const double P = a.P[n];
+        tileSync(barId, TT);
+        // ---- Phase::setMassFractions (Phase.cpp:342-360): clip, normalise
+        double sum = 0.0;
+        for (int k = j; k < K; k += NL) {
+            double y = t.cS[k * CTB_LDC];
+            y = y > 0.0 ? y : 0.0;
+            t.cS[k * CTB_LDC] = y;
+            sum += y;
+        }
+        red[j * CTB_TS + s] = sum;
+        tileSync(barId, TT);
+        sum = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) sum += red[l * CTB_TS + s];
+        const double invSum = 1.0 / sum;
+        sc.logT = log(sc.T);
+        sc.recipT = 1.0 / sc.T;
+        double sym = 0.0;
+        for (int k = j; k < K; k += NL) {
+            const double rmw = reinterpret_cast<const double*>(spTab + (size_t) k * sizeof(Sp2))[15];
+            const double ym = (t.cS[k * CTB_LDC] * invSum) * rmw;
+            t.cS[k * CTB_LDC] = ym;
+            sym += ym;
+        }
+        red[(NL + j) * CTB_TS + s] = sym;
+        tileSync(barId, TT);
+        sym = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) sym += red[(NL + l) * CTB_TS + s];
+        // setState_TP -> IdealGasPhase::setPressure (IdealGasPhase.h:352-354), molarDensity (Phase.cpp:597-600)
+        const double mmw = 1.0 / sym;
+        const double dens = P * mmw / (sc.T * CTB_GAS_CONSTANT);
+        sc.ctot = dens / mmw;
+        sc.P = CTB_GAS_CONSTANT * sc.ctot * sc.T;
+        sc.logP = needLogP ? log(sc.P) : 0.0;
+        // ---- concentrations, u = exp(-g'), v = c exp(g')
+        const double lnRT = sc.logT + tv.lnRp0;
+        bool risky = !(tv.maxAbsB * fabs(sc.logT) + tv.maxAbsEaR * fabs(sc.recipT) < 1e8);
+        for (int k = j; k < K; k += NL) {
+            double cp, h, sr, rmw;
+            nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
+            const double gp = (h - sr) + lnRT;
+            risky |= !(fabs(gp) <= CTB_SAFE_G);
+            const double ck = dens * t.cS[k * CTB_LDC];
+            t.cS[k * CTB_LDC] = ck;
+            t.uS[k * CTB_LDC] = expFast(-gp);
+            t.vS[k * CTB_LDC] = ck * expFast(gp);
+        }
+        if (risky) *safeFlag = 1;
+        tileSync(barId, TT);
+        const bool safe = *safeFlag != 0;
+        if (safe) {
+            // safe mode (rates_tile.cuh): the v rows hold g' itself
+            for (int k = j; k < K; k += NL) {
+                double cp, h, sr, rmw;
+                nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
+                t.vS[k * CTB_LDC] = (h - sr) + lnRT;
+            }
+            tileSync(barId, TT);
+        }
+        // the scratch may have covered the zero row of q (mechanisms with fewer than 2 NL reactions)
+        if (2 * NL > R && tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
+        ropPhaseTile<NL, false, ILP>(tv, t, sc, j, safe);
+        tileSync(barId, TT);
+        if (tid == 0) *safeFlag = 0;
+        gatherPhaseTile<NL>(tv, t, j, t.cS, CTB_LDC);
+        tileSync(barId, TT);
+        // ---- coalesced transposed store of the wdot rows
+        for (int i = tid; i < CTB_TS * K; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicK);
+            const int k = i - si * K;
+            if (si < nvalid) a.wdot[(n0 + si) * a.ldW + k] = c[k * CTB_LDC + si];
+        }
+        tileSync(barId, TT);
+    }
+}
 
 // --------------------------------------------------------------------------- rates, thread/state
 
@@ -257,6 +381,49 @@ static void launchRatesT(const DeviceMech& m, const RatesArgs& a, cudaStream_t s
     kern<<<grid, threads, smemBytes, stream>>>(v, m.dBlob, a, workAligned);
 }
 
+//! Bytes of shared memory one tile needs with NL reaction lanes.
+static size_t tileDoublesFor(const TileView& tv, int NL)
+{
+    size_t d = 3 * (size_t) tv.K * CTB_LDC + std::max((size_t) (tv.R + 1) * CTB_TS, 2 * (size_t) NL * CTB_TS);
+    return (d + 15) & ~(size_t) 15;
+}
+
+template <int W, int MAXT, int ILP>
+static bool launchRatesTileT(const DeviceMech& m, const RatesArgs& a, cudaStream_t stream)
+{
+    const TileView& tv = m.tile;
+    const size_t tableBytes = ((size_t) tv.bytes + 127) & ~(size_t) 127;
+    const size_t tileDoubles = tileDoublesFor(tv, 2 * W);
+    const size_t fixed = tableBytes + 128;
+    const size_t budget = (size_t) m.smemOptIn; // no static shared memory in this kernel
+    if (fixed + tileDoubles * 8 > budget) return false;
+    int tiles = (int) ((budget - fixed) / (tileDoubles * 8));
+    tiles = std::min(tiles, std::min(15, MAXT / (W * 32)));
+    if (tiles < 1) return false;
+    const long long nTiles = (a.N + CTB_TS - 1) / CTB_TS;
+    tiles = (int) std::min<long long>(tiles, std::max<long long>(1, (nTiles + m.numSMs - 1) / m.numSMs));
+    const size_t smemBytes = fixed + (size_t) tiles * tileDoubles * 8;
+    auto kern = ratesTileKernel<W, MAXT, ILP>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
+    const int grid = (int) std::max<long long>(1, std::min<long long>((nTiles + tiles - 1) / tiles, m.numSMs));
+    kern<<<grid, tiles * W * 32, smemBytes, stream>>>(tv, m.dBlob, a, (int) tileDoubles, (int) tableBytes);
+    return true;
+}
+
+//! The wdot-only path: tiles of 16 states. warpsPerTile: 0 = choose.
+static bool launchRatesTile(const DeviceMech& m, const RatesArgs& a, cudaStream_t stream)
+{
+    static const int forced = [] { const char* e = std::getenv("CTB_TILE_WARPS"); return e ? std::atoi(e) : 0; }();
+    static const int ilp = [] { const char* e = std::getenv("CTB_TILE_ILP"); return e ? std::atoi(e) : 1; }();
+    const int w = forced ? forced : 8;
+    switch (w * 10 + ilp) {
+    case 81: return launchRatesTileT<8, 768, 1>(m, a, stream);
+    case 82: return launchRatesTileT<8, 768, 2>(m, a, stream);
+    case 42: return launchRatesTileT<4, 512, 2>(m, a, stream);
+    default: return launchRatesTileT<4, 512, 1>(m, a, stream);
+    }
+}
+
 //! Threads per CTA of the thread-per-state kernels for this mechanism (0: does not fit).
 int threadKernelThreads(const DeviceMech& m, int arraysPerThread)
 {
@@ -288,6 +455,10 @@ void launchRates(const DeviceMech& m, const RatesArgs& a, bool full, cudaStream_
     // for >= 64 states per SM in shared memory.
     if (!full) {
         const char* force = std::getenv("CTB_RATES_KERNEL");
+        if (!(force && std::strcmp(force, "group") == 0) && !(force && std::strcmp(force, "thread") == 0)
+            && launchRatesTile(m, a, stream)) {
+            return;
+        }
         const int nth = threadKernelThreads(m, 3);
         if (nth > 0 && force && std::strcmp(force, "thread") == 0) {
             launchRatesThreadT<4>(m, a, nth, stream);

@@ -10,6 +10,7 @@ namespace ctb {
 //! A mechanism resident on one device.
 struct DeviceMech {
     MechView view;
+    TileView tile;                  // tables of the state-tile kernels (rates_tile.cuh)
     unsigned char* dBlob = nullptr; // device copy of PackedMech::blob
     int device = 0;
     int numSMs = 0;

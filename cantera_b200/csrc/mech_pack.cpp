@@ -322,6 +322,138 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     v.hasFractional = fractional ? 1 : 0;
     v.maxChebNT = maxChebNT;
     std::memcpy(bl.data.data() + v.o_view, &v, sizeof(MechView));
+
+    // ---- tile region (rates_tile.cuh): a second self-contained segment, offsets relative to it
+    {
+        while (bl.data.size() % 128) bl.data.push_back(0);
+        TileView& tv = pm.tv;
+        std::memset(&tv, 0, sizeof(tv));
+        tv.K = K; tv.R = R; tv.nRuns = (int32_t) runs.size(); tv.nTb = (int32_t) tbDefault.size();
+        tv.begin = (uint32_t) bl.data.size();
+        tv.magicK = (uint32_t) ((0x100000000ULL + (unsigned long long) K - 1) / (unsigned long long) K);
+        tv.lnRp0 = std::log(6.02214076e26 * 1.380649e-23 / t.p_ref);
+        for (int e = 0; e < R; e++) {
+            tv.maxAbsB = std::max(tv.maxAbsB, std::abs(b[e]));
+            tv.maxAbsEaR = std::max(tv.maxAbsEaR, std::abs(EaR[e]));
+        }
+        Blob tb;
+        std::vector<Sp2> sp(K);
+        for (int k = 0; k < K; k++) {
+            for (int j = 0; j < 7; j++) { sp[k].low[j] = low[7 * k + j]; sp[k].high[j] = high[7 * k + j]; }
+            sp[k].tmid = tmid[k];
+            sp[k].rmolwt = rmolwt[k];
+        }
+        std::vector<Rx2> rx(R);
+        std::vector<double> auxMult;
+        for (int e = 0; e < R; e++) {
+            Rx2& x = rx[e];
+            std::memset(&x, 0, sizeof(x));
+            const bool arr = rec[e].cls == CLS_ARR || rec[e].cls == CLS_ARR_CONST;
+            x.A = arr ? A[e] * mult[e] : A[e];
+            x.b = b[e]; x.EaR = EaR[e];
+            // unit sides: heaviest molecule first, so that pairedProduct (rates_tile.cuh) multiplies
+            // factors of similar magnitude
+            uint16_t sr[3] = {rec[e].r[0], rec[e].r[1], rec[e].r[2]}, spd[3] = {rec[e].p[0], rec[e].p[1], rec[e].p[2]};
+            auto heavyFirst = [&](uint8_t cnt, uint16_t* sl) {
+                if (cnt == SIDE_GENERAL) return;
+                std::stable_sort(sl, sl + cnt, [&](uint16_t a, uint16_t b2) { return molwt[a] > molwt[b2]; });
+            };
+            heavyFirst(rec[e].nr, sr);
+            heavyFirst(rec[e].np, spd);
+            auto slot = [&](uint8_t cnt, const uint16_t* sl, int i) -> uint32_t {
+                if (cnt == SIDE_GENERAL) return sl[i];
+                return sl[i] == 0xFFFF ? 0u : (uint32_t) sl[i] * CTB_LDC * 8u;
+            };
+            x.r0 = slot(rec[e].nr, sr, 0); x.r1 = slot(rec[e].nr, sr, 1); x.r2 = slot(rec[e].nr, sr, 2);
+            x.p0 = slot(rec[e].np, spd, 0); x.p1 = slot(rec[e].np, spd, 1); x.p2 = slot(rec[e].np, spd, 2);
+            x.nr = rec[e].nr; x.np = rec[e].np; x.cls = rec[e].cls; x.flags = rec[e].flags;
+            x.tbIdx = tbIdx[e]; x.auxIdx = auxIdx[e];
+        }
+        {
+            // aux ordinals are per class family (falloff / plog / chebyshev count separately): one
+            // multiplier table per family, concatenated: [falloff | plog | cheb]
+            const int nF = (int) (fallLow.size() / 3), nP = (int) plogPtr.size() - 1, nC = (int) chebPtr.size() - 1;
+            auxMult.assign((size_t) nF + nP + nC + 1, 1.0);
+            for (int e = 0; e < R; e++) {
+                if (auxIdx[e] < 0) continue;
+                const int c = rec[e].cls;
+                const int base = (c >= CLS_LINDEMANN && c <= CLS_TSANG) ? 0 : (c == CLS_PLOG ? nF : nF + nP);
+                auxMult[(size_t) base + auxIdx[e]] = mult[e];
+                rx[e].auxMultIdx = (uint32_t) (base + auxIdx[e]);
+            }
+        }
+        // gather entries: per species [+1 pairs][-1 pairs], gen entries aside
+        std::vector<uint32_t> gEnt2;
+        std::vector<GGen2> gGen2;
+        std::vector<GSp2> gsp(K);
+        const uint32_t zeroRow = (uint32_t) R * CTB_TS * 8;
+        for (int k = 0; k < K; k++) {
+            GSp2& g = gsp[k];
+            g.k = (uint16_t) k;
+            g.start = (uint32_t) (gEnt2.size() * 4);
+            g.genStart = (uint32_t) gGen2.size();
+            std::vector<uint32_t> plus, minus;
+            for (auto& [e, nu] : lists[k]) {
+                if (nu == 0.0) continue;
+                const uint32_t off = (uint32_t) e * CTB_TS * 8;
+                const double an = std::abs(nu);
+                if (std::fmod(an, 1.0) == 0.0 && an <= 3.0) {
+                    for (int r = 0; r < (int) an; r++) (nu > 0 ? plus : minus).push_back(off);
+                } else {
+                    gGen2.push_back(GGen2{off, 0, nu});
+                }
+            }
+            while (plus.size() % 4) plus.push_back(zeroRow);
+            while (minus.size() % 4) minus.push_back(zeroRow);
+            if (plus.size() / 4 > 65535 || minus.size() / 4 > 65535) throw std::runtime_error("packMechanism: gather list too long");
+            g.nPlus4 = (uint16_t) (plus.size() / 4);
+            g.nMinus4 = (uint16_t) (minus.size() / 4);
+            g.nGen = (uint16_t) (gGen2.size() - g.genStart);
+            gEnt2.insert(gEnt2.end(), plus.begin(), plus.end());
+            gEnt2.insert(gEnt2.end(), minus.begin(), minus.end());
+        }
+        tv.hasGen = gGen2.empty() ? 0 : 1;
+        tv.hasPdep = (plogLogP.empty() && chebCoef.empty()) ? 0 : 1;
+        tv.o_sp = tb.put(sp); tv.o_rx = tb.put(rx); tv.o_runs = tb.put(runs);
+        tv.o_gEnt = tb.put(gEnt2); tv.o_gGen = tb.put(gGen2);
+        for (int d = 0; d < CTB_TILE_DEALS; d++) {
+            const int NL = 8 << d;
+            std::vector<int> order(K);
+            std::iota(order.begin(), order.end(), 0);
+            auto cost = [&](int k) { return 2 * ((long long) gsp[k].nPlus4 + gsp[k].nMinus4) + gsp[k].nGen + 3; };
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b2) { return cost(a) > cost(b2); });
+            std::vector<std::vector<int>> lane(NL);
+            std::vector<long long> load(NL, 0);
+            for (int k : order) {
+                int best = 0;
+                for (int l = 1; l < NL; l++) if (load[l] < load[best]) best = l;
+                lane[best].push_back(k);
+                load[best] += cost(k);
+            }
+            std::vector<GSp2> dealt;
+            std::vector<int32_t> lanePtr(NL + 1, 0);
+            for (int l = 0; l < NL; l++) {
+                for (int k : lane[l]) dealt.push_back(gsp[k]);
+                lanePtr[l + 1] = (int32_t) dealt.size();
+            }
+            tv.o_gSp[d] = tb.put(dealt);
+            tv.o_gLane[d] = tb.put(lanePtr);
+        }
+        tv.o_tbDefault = tb.put(tbDefault); tv.o_tbPtr = tb.put(tbPtr); tv.o_tbSp = tb.put(tbSp); tv.o_tbEff = tb.put(tbEff);
+        tv.o_fallLow = tb.put(fallLow); tv.o_fallCoef = tb.put(fallCoef); tv.o_auxMult = tb.put(auxMult);
+        tv.o_plogPtr = tb.put(plogPtr); tv.o_plogLogP = tb.put(plogLogP); tv.o_plogA = tb.put(plogA);
+        tv.o_plogB = tb.put(plogB); tv.o_plogEaR = tb.put(plogEaR);
+        tv.o_chebPtr = tb.put(chebPtr); tv.o_chebDim = tb.put(chebDim); tv.o_chebLim = tb.put(chebLim);
+        tv.o_chebCoef = tb.put(chebCoef);
+        tv.o_genPtr = tb.put(genPtr); tv.o_genSp = tb.put(genSp); tv.o_genStoich = tb.put(genStoich);
+        tv.o_genOrder = tb.put(genOrder);
+        tb.finish();
+        tv.bytes = (uint32_t) tb.data.size();
+        bl.data.insert(bl.data.end(), tb.data.begin(), tb.data.end());
+        bl.finish();
+        v.bytes = (uint32_t) bl.data.size();
+        std::memcpy(bl.data.data() + v.o_view, &v, sizeof(MechView));
+    }
     pm.blob = std::move(bl.data);
     return pm;
 }

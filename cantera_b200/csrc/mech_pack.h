@@ -137,8 +137,89 @@ struct MechView {
     uint32_t hotBytes;                      // prefix staged into shared memory (multiple of 16)
 };
 
+// ------------------------------------------------------------------------------------------------
+// Tile region: the tables of the state-tile kernels (rates_tile.cuh). A TILE is CTB_TS states whose
+// per-species / per-reaction values sit in shared memory as rows [index][CTB_TS]; the lanes of a
+// half-warp are the 16 states of one tile working on ONE reaction (or species), so every table
+// read below is a broadcast and every row access is conflict-free. The region is a second,
+// self-contained, 128-byte aligned segment of the blob (offsets relative to its start) that the
+// tile kernels stage into shared memory with one TMA bulk copy.
+// ------------------------------------------------------------------------------------------------
+#define CTB_TS 16               // states per tile
+#define CTB_LDC (CTB_TS + 1)    // padded leading dimension of the c / wdot rows (transposed global I/O)
+
+// species record, 128 bytes: NASA7 low range, Tmid, high range, 1/W (NasaPoly2.h:105-112)
+struct Sp2 {
+    double low[7];
+    double tmid;
+    double high[7];
+    double rmolwt;
+};
+static_assert(sizeof(Sp2) == 128, "Sp2 must be 128 bytes");
+
+// reaction record, 64 bytes (four 128-bit words; a fast run reads the first two or three). A
+// already carries the reaction's multiplier for the Arrhenius classes. The species slots are BYTE
+// OFFSETS of the species' row in the c / u / v arrays (k * CTB_LDC * 8) so that an address is one
+// add; a SIDE_GENERAL side keeps the index of its general-side entry in slot 0.
+struct Rx2 {
+    double A, b;              // word 0
+    double EaR;               // word 1
+    uint32_t r0, r1;
+    uint32_t r2, p0, p1, p2;  // word 2
+    uint8_t nr, np, cls, flags; // word 3
+    int16_t tbIdx, auxIdx;
+    uint32_t auxMultIdx;      // ordinal into the auxMult table (non-Arrhenius classes)
+    uint32_t pad;
+};
+static_assert(sizeof(Rx2) == 64, "Rx2 must be 64 bytes");
+
+// gather record of one species, 16 bytes: its entries are QUADS of 32-bit byte offsets of q rows
+// (execution index * CTB_TS * 8), nu = +1 entries first, then nu = -1 entries; |nu| = 2, 3 repeat the
+// entry, counts are padded to a multiple of four with the offset of the all-zero row q[R].
+// Everything else (fractional or large coefficients) goes through the gen list with an explicit double.
+struct GSp2 {
+    uint32_t start;          // byte offset of the first quad inside the entry table (multiple of 16)
+    uint16_t nPlus4, nMinus4; // number of QUADS
+    uint16_t k;              // species
+    uint16_t nGen;
+    uint32_t genStart;       // index of the first gen entry
+};
+static_assert(sizeof(GSp2) == 16, "GSp2 must be 16 bytes");
+struct GGen2 {
+    uint32_t off;
+    uint32_t pad;
+    double nu;
+};
+static_assert(sizeof(GGen2) == 16, "GGen2 must be 16 bytes");
+
+#define CTB_TILE_DEALS 2 // gather deals for 8 and 16 reaction lanes per state
+struct TileView {
+    int32_t K, R, nRuns, nTb;
+    uint32_t begin;   // offset of the region inside the blob (multiple of 128)
+    uint32_t bytes;   // size of the region (multiple of 16)
+    uint32_t magicK;  // ceil(2^32 / K): i / K == __umulhi(i, magicK) for i < 65536
+    int32_t hasGen;   // any GGen2 entries
+    int32_t hasPdep;  // any Plog / Chebyshev reaction (the kernels then form log P)
+    int32_t pad0;
+    double lnRp0;     // log(GasConstant / p_ref): g' = (h/RT - s/R) + log T + lnRp0
+    double maxAbsB, maxAbsEaR; // over all Arrhenius parameter sets: bound of |b log T - (Ea/R)/T| per state
+    uint32_t o_sp;    // Sp2[K]
+    uint32_t o_rx;    // Rx2[R]
+    uint32_t o_runs;  // RunRec[nRuns]
+    uint32_t o_gEnt;  // uint32 pairs
+    uint32_t o_gGen;  // GGen2[]
+    uint32_t o_gSp[CTB_TILE_DEALS];   // GSp2[K], species in lane order of the deal
+    uint32_t o_gLane[CTB_TILE_DEALS]; // int32[NL + 1]
+    uint32_t o_tbDefault, o_tbPtr, o_tbSp, o_tbEff; // third bodies (tbSp: uint16 species)
+    uint32_t o_fallLow, o_fallCoef, o_auxMult;      // falloff tables; multiplier of non-Arrhenius classes by aux ordinal
+    uint32_t o_plogPtr, o_plogLogP, o_plogA, o_plogB, o_plogEaR;
+    uint32_t o_chebPtr, o_chebDim, o_chebLim, o_chebCoef;
+    uint32_t o_genPtr, o_genSp, o_genStoich, o_genOrder;
+};
+
 struct PackedMech {
     MechView v;
+    TileView tv;
     std::vector<unsigned char> blob;
     std::vector<int32_t> perm;    // execution -> reference
     std::vector<int32_t> invPerm; // reference -> execution

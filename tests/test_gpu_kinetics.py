@@ -112,6 +112,29 @@ def test_rates_vs_oracle_random(case, n, kin_cache, oracle_lib):
     assert _rel(w.cpu().numpy(), o["wdot"], sc) <= TOL
 
 
+@pytest.mark.parametrize("case,Tlo,Thi", [("gri30", 120.0, 400.0), ("nDodecane", 150.0, 600.0), ("nDodecane", 250.0, 3500.0)])
+def test_rates_extreme_temperatures(case, Tlo, Thi, kin_cache, oracle_lib):
+    """Very low temperatures make |g'_k| = |mu0_k/RT - ln(P/RT)| exceed the range in which the tile
+    kernel's per-species factors exp(+-g') can be multiplied safely: such tiles switch to the safe
+    mode (rates_tile.cuh: one exp of the summed g' per reaction, the reference's own formula). The
+    batch mixes tiles of both kinds; parity with the oracle as everywhere else."""
+    kin = kin_cache(case)
+    m = oracle_lib.OracleMech(MECHS[case])
+    K = m.K
+    n = 2000
+    rng = np.random.default_rng(5)
+    T = rng.uniform(Tlo, Thi, n)
+    P = 101325.0 * rng.uniform(0.1, 50, n)
+    Y = rng.uniform(0, 1, (n, K))
+    Y /= Y.sum(axis=1, keepdims=True)
+    o = m.rates(T, P, Y, want=("wdot", "cdot", "ddot"))
+    sc = o["cdot"] + o["ddot"]
+    w = kin.net_production_rates(T, P, Y)
+    assert np.all(np.isfinite(w))
+    live = sc > 1e-250  # below that the terms themselves are denormal
+    assert float(np.max(np.abs(w - o["wdot"])[live] / sc[live])) <= TOL
+
+
 def test_multiplier_and_errors(kin_cache, oracle_lib):
     from cantera_b200 import CtbError
     kin = kin_cache("h2o2")

@@ -49,6 +49,16 @@ def main(cases):
             dt = time.perf_counter() - t0
             assert np.all(net.status() == 0), np.unique(net.status(), return_counts=True)
             report(tag + " %s" % (net.effective_tolerances(),), T, Y, net.ignition_delay(), net.solver_stats().sum(axis=0), dt)
+            # the worst reactors, with the reference's own distance from its converged twin beside ours
+            tolc = 1e-6 * np.abs(Yc) + 1e-12
+            ours = (np.abs(Y - Yc) / tolc).max(axis=1)
+            refc = (np.abs(Yc - Yt) / tolc).max(axis=1)
+            ourt = (np.abs(Y - Yt) / tolc).max(axis=1)
+            tig = net.ignition_delay()
+            for i in np.argsort(-ours)[:10]:
+                print("    reactor %4d T0 %7.1f P %5.1f atm Tend %7.1f tign ref %.6e tight %.6e ours %.6e | Y/tol ours-ref %.3f ref-conv %.3f ours-conv %.3f | dT ours-ref %.2e ref-conv %.2e%s" % (
+                    i, g["T"][i], g["P"][i] / 101325, g["Tend"][i], g["tign"][i], t["tign"][i], tig[i], ours[i], refc[i], ourt[i],
+                    T[i] - g["Tend"][i], g["Tend"][i] - t["Tend"][i], " (front)" if front[i] else ""))
             net.close()
         kin.close()
 
