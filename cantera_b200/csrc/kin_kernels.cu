@@ -208,28 +208,12 @@ __global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const
         sc.P = CTB_GAS_CONSTANT * sc.ctot * sc.T;
         sc.logP = needLogP ? log(sc.P) : 0.0;
         // ---- concentrations, u = exp(-g'), v = c exp(g')
-        const double lnRT = sc.logT + tv.lnRp0;
-        bool risky = !(tv.maxAbsB * fabs(sc.logT) + tv.maxAbsEaR * fabs(sc.recipT) < 1e8);
-        for (int k = j; k < K; k += NL) {
-            double cp, h, sr, rmw;
-            nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
-            const double gp = (h - sr) + lnRT;
-            risky |= !(fabs(gp) <= CTB_SAFE_G);
-            const double ck = dens * t.cS[k * CTB_LDC];
-            t.cS[k * CTB_LDC] = ck;
-            t.uS[k * CTB_LDC] = expFast(-gp);
-            t.vS[k * CTB_LDC] = ck * expFast(gp);
-        }
-        if (risky) *safeFlag = 1;
+        double unused = 0.0;
+        if (speciesPhaseTile<NL, false>(tv, t, sc, 1.0, dens, j, unused)) *safeFlag = 1;
         tileSync(barId, TT);
         const bool safe = *safeFlag != 0;
         if (safe) {
-            // safe mode (rates_tile.cuh): the v rows hold g' itself
-            for (int k = j; k < K; k += NL) {
-                double cp, h, sr, rmw;
-                nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
-                t.vS[k * CTB_LDC] = (h - sr) + lnRT;
-            }
+            speciesPhaseSafeTile<NL>(tv, t, sc, j);
             tileSync(barId, TT);
         }
         // the scratch may have covered the zero row of q (mechanisms with fewer than 2 NL reactions)
@@ -237,7 +221,7 @@ __global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const
         ropPhaseTile<NL, false, ILP>(tv, t, sc, j, safe);
         tileSync(barId, TT);
         if (tid == 0) *safeFlag = 0;
-        gatherPhaseTile<NL>(tv, t, j, t.cS, CTB_LDC);
+        gatherPhaseTile<NL>(tv, t, j, [&](int k, double w) { t.cS[k * CTB_LDC] = w; });
         tileSync(barId, TT);
         // ---- coalesced transposed store of the wdot rows
         for (int i = tid; i < CTB_TS * K; i += TT) {

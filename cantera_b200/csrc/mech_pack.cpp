@@ -414,7 +414,8 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         }
         tv.hasGen = gGen2.empty() ? 0 : 1;
         tv.hasPdep = (plogLogP.empty() && chebCoef.empty()) ? 0 : 1;
-        tv.o_sp = tb.put(sp); tv.o_rx = tb.put(rx); tv.o_runs = tb.put(runs);
+        tv.magicN = (uint32_t) ((0x100000000ULL + (unsigned long long) K) / (unsigned long long) (K + 1));
+        tv.o_sp = tb.put(sp); tv.o_molwt = tb.put(molwt); tv.o_rx = tb.put(rx); tv.o_runs = tb.put(runs);
         tv.o_gEnt = tb.put(gEnt2); tv.o_gGen = tb.put(gGen2);
         for (int d = 0; d < CTB_TILE_DEALS; d++) {
             const int NL = 8 << d;

@@ -204,6 +204,8 @@ struct TileView {
     double lnRp0;     // log(GasConstant / p_ref): g' = (h/RT - s/R) + log T + lnRp0
     double maxAbsB, maxAbsEaR; // over all Arrhenius parameter sets: bound of |b log T - (Ea/R)/T| per state
     uint32_t o_sp;    // Sp2[K]
+    uint32_t o_molwt; // double[K] molecular weights (reactor kernels)
+    uint32_t magicN;  // ceil(2^32 / (K + 1))
     uint32_t o_rx;    // Rx2[R]
     uint32_t o_runs;  // RunRec[nRuns]
     uint32_t o_gEnt;  // uint32 pairs

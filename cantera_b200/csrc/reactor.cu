@@ -224,7 +224,11 @@ void BatchReactorNet::eval(double* ydot, long long bufLen, int memspace)
         m_io.reserve(sizeof(double) * (size_t) need);
         d = m_io.as<double>();
     }
-    launchReactorEval(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st);
+    // the kernel the integrator itself uses (tile form) wherever the mechanism fits it
+    const bool groupRhs = std::getenv("CTB_RHS_KERNEL") && std::string(std::getenv("CTB_RHS_KERNEL")) == "group";
+    if (groupRhs || !launchReactorEvalTile(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st)) {
+        launchReactorEval(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st);
+    }
     cudaCheck(cudaGetLastError(), "eval launch");
     if (memspace != CTB_DEVICE) {
         cudaCheck(cudaMemcpyAsync(ydot, d, sizeof(double) * need, cudaMemcpyDeviceToHost, st), "D2H ydot");

@@ -63,6 +63,9 @@ void launchReactorContents(const DeviceMech& m, long long N, const double* y, do
 //! ydot = ReactorNet::eval at the current solution vectors
 void launchReactorEval(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
                        cudaStream_t stream);
+//! The same through the tile kernel (reactor_batch.cu); false if the mechanism does not fit it
+bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+                           cudaStream_t stream);
 //! doubles of integrator memory per reactor
 long long reactorHistDoubles(int neq);
 

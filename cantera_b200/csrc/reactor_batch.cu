@@ -16,6 +16,7 @@
 // with the per-slot integrator memory in HBM. Tens of thousands of reactors are in flight per
 // round, so the chemistry runs at the throughput of the rates kernels.
 #include "bdf_batch.cuh"
+#include "rates_tile.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -197,6 +198,149 @@ __global__ void __launch_bounds__(512) batchRhsKernel(const MechView v, const un
     }
 }
 
+//! The same right-hand side for TILES of 16 slots (rates_tile.cuh): W warps per tile, a half-warp is the
+//! 16 slots of the tile working on one reaction / species. IdealGasConstPressureMoleReactor::updateState
+//! + eval (IdealGasConstPressureMoleReactor.cpp:38-106) as in reactorRhs of bdf.cuh.
+//! Shared memory: [tile tables (TMA)] [mbarrier, flags] [per tile: c rows, u rows, v rows, q rows, scratch].
+//! Where the tile kernel finds its states: the integrator's slots ...
+struct SlotIO {
+    SlotMem mem;
+    __device__ __forceinline__ long long count() const { return mem.S; }
+    __device__ __forceinline__ bool active(long long i) const { return mem.pc[i] != PC_IDLE; }
+    __device__ __forceinline__ const double* y(long long i) const { return mem.vec((int) i) + 8 * mem.n; }
+    __device__ __forceinline__ double* f(long long i) const { return mem.vec((int) i) + 9 * mem.n; }
+    __device__ __forceinline__ double P(long long i) const { return mem.ctl((int) i)->P; }
+};
+//! ... or plain rows y[N][K+1] (ReactorNet::eval, ctb_reactornet_eval)
+struct RowIO {
+    long long N;
+    int n;
+    const double* yRows;
+    const double* Pv;
+    double* ydot;
+    __device__ __forceinline__ long long count() const { return N; }
+    __device__ __forceinline__ bool active(long long) const { return true; }
+    __device__ __forceinline__ const double* y(long long i) const { return yRows + i * n; }
+    __device__ __forceinline__ double* f(long long i) const { return ydot + i * n; }
+    __device__ __forceinline__ double P(long long i) const { return Pv[i]; }
+};
+
+template <int W, int MAXT, class IO>
+__global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
+                                                           const IO io, const int tileDoubles, const int tableBytes)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + tableBytes);
+    tmaStage(smem, gblob + tv.begin, tv.bytes, bar);
+    constexpr int TT = W * 32, NL = 2 * W;
+    const int ti = threadIdx.x / TT, tid = threadIdx.x % TT;
+    const int tilesPerCta = blockDim.x / TT;
+    const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
+    const int K = tv.K, R = tv.R, n = K + 1;
+    double* c = reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles;
+    double* u = c + K * CTB_LDC;
+    double* v = u + K * CTB_LDC;
+    double* q = v + K * CTB_LDC;
+    double* red = q;                                   // [3][NL][16]: dead before the q rows are written
+    double* red2 = q + max((R + 1) * CTB_TS, 3 * NL * CTB_TS); // [NL][16] + Trow[16]: live while the q rows are read
+    double* Trow = red2 + NL * CTB_TS;
+    Tile t;
+    t.tp = smem;
+    t.cS = c + s; t.uS = u + s; t.vS = v + s; t.qS = q + s;
+    const double* molwt = CTB_TAB(double, smem, tv.o_molwt);
+    volatile int* safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
+    if (tid == 0) *safeFlag = 0;
+    if (tid < CTB_TS) q[R * CTB_TS + tid] = 0.0; // the all-zero row the padded gather entries point to
+    const int barId = 1 + ti;
+    const long long S = io.count();
+    const long long nTiles = (S + CTB_TS - 1) / CTB_TS;
+    for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
+        const long long sl0 = tile * CTB_TS;
+        const long long sl = min(sl0 + s, S - 1);
+        const bool valid = sl0 + s < S && io.active(sl);
+        // every warp of the tile holds all 16 slots: the vote is the same in all of them
+        if (!__any_sync(0xffffffffu, valid)) continue;
+        // ---- transposed load of the requested states y = [T, n_1..n_K]; idle slots get a benign state
+        for (int i = tid; i < CTB_TS * n; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicN);
+            const int e = i - si * n;
+            const long long ss = min(sl0 + si, S - 1);
+            const bool ok = sl0 + si < S && io.active(ss);
+            const double val = ok ? io.y(ss)[e] : (e == 0 ? 1000.0 : 1.0);
+            if (e == 0) Trow[si] = val; else c[(e - 1) * CTB_LDC + si] = val;
+        }
+        const double P = valid ? io.P(sl) : 101325.0;
+        if (2 * NL > R && tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
+        tileSync(barId, TT);
+        TileScalars sc;
+        sc.T = Trow[s];
+        // ---- Phase::setMolesNoTruncate (Phase.cpp:550-568): no clipping
+        double totalMoles = 0.0, totalMass = 0.0;
+        for (int k = j; k < K; k += NL) {
+            const double nk = t.cS[k * CTB_LDC];
+            totalMoles += nk;
+            totalMass += nk * molwt[k];
+        }
+        red[j * CTB_TS + s] = totalMoles;
+        red[(NL + j) * CTB_TS + s] = totalMass;
+        tileSync(barId, TT);
+        totalMoles = 0.0; totalMass = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) { totalMoles += red[l * CTB_TS + s]; totalMass += red[(NL + l) * CTB_TS + s]; }
+        const double mmw = totalMass / totalMoles;
+        const double f2 = 1.0 / (mmw * totalMoles);
+        const double dens = P * mmw / (sc.T * CTB_GAS_CONSTANT);
+        sc.ctot = dens / mmw;
+        sc.P = CTB_GAS_CONSTANT * sc.ctot * sc.T;
+        sc.logT = log(sc.T);
+        sc.recipT = 1.0 / sc.T;
+        sc.logP = tv.hasPdep ? log(sc.P) : 0.0;
+        // c rows hold n_k: ym = n_k W_k f2 is the mass fraction over W_k, i.e. n_k f2 * ... (reactorRhs: ym = y f2)
+        double sumq = 0.0;
+        if (speciesPhaseTile<NL, true>(tv, t, sc, f2, dens, j, sumq)) *safeFlag = 1;
+        red[(2 * NL + j) * CTB_TS + s] = sumq;
+        tileSync(barId, TT);
+        const bool safe = *safeFlag != 0;
+        if (safe) speciesPhaseSafeTile<NL>(tv, t, sc, j);
+        sumq = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) sumq += red[(2 * NL + l) * CTB_TS + s];
+        tileSync(barId, TT); // every lane has read the scratch (it aliases the q rows)
+        if (2 * NL > R && tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
+        ropPhaseTile<NL, true, 1>(tv, t, sc, j, safe);
+        tileSync(barId, TT);
+        if (tid == 0) *safeFlag = 0;
+        // ---- ydot: species rows V wdot_k into the c rows, temperature row from sum_k wdot_k h_k
+        const double vol = totalMass / dens;
+        const double cp_mole = CTB_GAS_CONSTANT * (mmw * sumq);
+        const double totalCp = totalMass * (cp_mole / mmw);
+        const double RT = sc.T * CTB_GAS_CONSTANT;
+        double mcpdTdt = 0.0;
+        const unsigned char* spTab = smem + tv.o_sp;
+        gatherPhaseTile<NL>(tv, t, j, [&](int k, double wdot) {
+            double cp, h, sr, rmw;
+            nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
+            mcpdTdt -= wdot * (h * RT) * vol;
+            t.cS[k * CTB_LDC] = wdot * vol;
+        });
+        red2[j * CTB_TS + s] = mcpdTdt;
+        tileSync(barId, TT);
+        if (j == 0) {
+            mcpdTdt = 0.0;
+#pragma unroll
+            for (int l = 0; l < NL; l++) mcpdTdt += red2[l * CTB_TS + s];
+            if (valid) io.f(sl)[0] = mcpdTdt / totalCp;
+        }
+        for (int i = tid; i < CTB_TS * K; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicK);
+            const int k = i - si * K;
+            const long long ss = sl0 + si;
+            if (ss < S && io.active(ss)) io.f(ss)[1 + k] = c[k * CTB_LDC + si];
+        }
+        tileSync(barId, TT);
+    }
+}
+
 //! J = d(ydot)/dy at the slot's requested state, for the slots the controller flagged in this round.
 //! One NamedGroup of NT threads per slot; J goes to the slot's matrix region (column-major n x n),
 //! where batchInvertKernel turns it into (I - gamma J)^-1.
@@ -341,6 +485,39 @@ __global__ void __launch_bounds__(RP * SPLIT) batchInvertKernel(const SlotMem me
     if (mem.prof && tid == 0) atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 5), (unsigned long long) (clock64() - tk));
 }
 
+//! Launch description of the tile right-hand-side kernel; tiles == 0: the mechanism does not fit.
+struct RhsTilePlan {
+    int tiles = 0, grid = 0;
+    size_t smemBytes = 0, tileDoubles = 0, tableBytes = 0;
+};
+constexpr int RHS_TILE_W = 8, RHS_TILE_MAXT = 768;
+
+RhsTilePlan planRhsTile(const DeviceMech& m, long long S)
+{
+    RhsTilePlan p;
+    const TileView& tv = m.tile;
+    constexpr int NL = 2 * RHS_TILE_W;
+    p.tableBytes = ((size_t) tv.bytes + 127) & ~(size_t) 127;
+    const size_t d = 3 * (size_t) tv.K * CTB_LDC + std::max((size_t) (tv.R + 1) * CTB_TS, 3 * (size_t) NL * CTB_TS)
+                     + (size_t) NL * CTB_TS + CTB_TS;
+    p.tileDoubles = (d + 15) & ~(size_t) 15;
+    const size_t fixed = p.tableBytes + 128;
+    const size_t budget = (size_t) m.smemOptIn;
+    if (fixed + p.tileDoubles * 8 > budget) return p;
+    int tiles = (int) ((budget - fixed) / (p.tileDoubles * 8));
+    tiles = std::min(tiles, std::min(15, RHS_TILE_MAXT / (RHS_TILE_W * 32)));
+    const long long nTiles = (S + CTB_TS - 1) / CTB_TS;
+    tiles = (int) std::min<long long>(tiles, std::max<long long>(1, (nTiles + m.numSMs - 1) / m.numSMs));
+    p.tiles = tiles;
+    p.smemBytes = fixed + (size_t) tiles * p.tileDoubles * 8;
+    p.grid = (int) std::max<long long>(1, std::min<long long>((nTiles + tiles - 1) / tiles, m.numSMs));
+    cudaFuncSetAttribute(batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, SlotIO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int) p.smemBytes);
+    cudaFuncSetAttribute(batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, RowIO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int) p.smemBytes);
+    return p;
+}
+
 template <int NT>
 bool launchJacT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 {
@@ -401,6 +578,18 @@ void launchInvert(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 
 } // namespace
 
+bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+                           cudaStream_t stream)
+{
+    if (N <= 0) return true;
+    const RhsTilePlan tp = planRhsTile(m, N);
+    if (tp.tiles == 0) return false;
+    RowIO io = {N, m.tile.K + 1, y, P, ydot};
+    batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, RowIO><<<tp.grid, tp.tiles * RHS_TILE_W * 32, tp.smemBytes, stream>>>(
+        m.tile, m.dBlob, io, (int) tp.tileDoubles, (int) tp.tableBytes);
+    return true;
+}
+
 long long batchSlotCap(const DeviceMech& m, int neq)
 {
     SlotMem tmp = {};
@@ -458,6 +647,9 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     const size_t rhsSmem = rhsFixed + (size_t) rhsGroups * rhsGroupDoubles * 8;
     cudaFuncSetAttribute(batchRhsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) rhsSmem);
     const int rhsGrid = (int) std::max<long long>(1, std::min<long long>((S + rhsGroups - 1) / rhsGroups, m.numSMs));
+    // the tile kernel (rates_tile.cuh) wherever the mechanism's tables and one tile fit in shared memory
+    const bool groupRhs = std::getenv("CTB_RHS_KERNEL") && std::string(std::getenv("CTB_RHS_KERNEL")) == "group";
+    const RhsTilePlan tp = groupRhs ? RhsTilePlan() : planRhsTile(m, S);
 
     // ---- control kernel: one shared-memory [ctl | vec] buffer per warp
     int ctlWarps = (int) std::min<size_t>(CTB_CTL_WARPS, (budget - 256) / mem.oM);
@@ -488,7 +680,12 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
         if (e5) cudaEventRecord(e5[0], stream);
         ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem);
         if (e5) cudaEventRecord(e5[1], stream);
-        batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
+        if (tp.tiles > 0) {
+            batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, SlotIO><<<tp.grid, tp.tiles * RHS_TILE_W * 32, tp.smemBytes, stream>>>(
+                m.tile, m.dBlob, SlotIO{mem}, (int) tp.tileDoubles, (int) tp.tableBytes);
+        } else {
+            batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
+        }
         if (e5) cudaEventRecord(e5[2], stream);
         launchJac(m, mem, stream);
         if (e5) cudaEventRecord(e5[3], stream);
