@@ -237,7 +237,8 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
     a.ddCi = ddCi; a.skipThirdBodies = m_skip3b; a.skipFalloff = m_skipFalloff;
     if (memspace == CTB_DEVICE) {
         a.N = N; a.T = T; a.P = P; a.Y = Y; a.ldY = ldY; a.jac = jac;
-        launchJac(m_dev, a, stream());
+        m_jacScratch[NSTAGE].reserve(jacScratchBytes(m_dev));
+        launchJac(m_dev, a, stream(), m_jacScratch[NSTAGE].p);
         cudaCheck(cudaGetLastError(), "jacKernel launch");
         return;
     }
@@ -245,7 +246,10 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
     const size_t perState = sizeof(double) * (2 + (size_t) K + (size_t) K * K);
     long long chunk = std::max<long long>(256, std::min<long long>(N, (long long) ((128u << 20) / perState)));
     chunk = std::min<long long>(chunk, std::max<long long>(256, (N + 31) / 32));
-    for (int b = 0; b < NSTAGE; b++) m_stage[b].reserve((size_t) chunk * perState);
+    for (int b = 0; b < NSTAGE; b++) {
+        m_stage[b].reserve((size_t) chunk * perState);
+        m_jacScratch[b].reserve(jacScratchBytes(m_dev));
+    }
     int b = 0;
     for (long long n0 = 0; n0 < N; n0 += chunk, b = (b + 1) % NSTAGE) {
         const long long n = std::min(chunk, N - n0);
@@ -259,7 +263,7 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
         cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
         copyRows(dY, K, Y + n0 * ldY, ldY, K, n, cudaMemcpyHostToDevice, st, "H2D Y");
         a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.jac = dJ;
-        launchJac(m_dev, a, st);
+        launchJac(m_dev, a, st, m_jacScratch[b].p);
         cudaCheck(cudaGetLastError(), "jacKernel launch");
         cudaCheck(cudaMemcpyAsync(jac + n0 * (long long) K * K, dJ, sizeof(double) * n * K * K,
                                   cudaMemcpyDeviceToHost, st), "D2H jac");

@@ -88,6 +88,7 @@ private:
     bool m_skip3b = false, m_skipFalloff = false;
     double m_rtolDelta = 1e-8;
     DevBuf m_stage[NSTAGE]; // device staging for host-memory calls
+    DevBuf m_jacScratch[NSTAGE + 1]; // per-stream scratch of the Jacobian tile kernel (last: the handle's own stream)
 };
 
 } // namespace ctb

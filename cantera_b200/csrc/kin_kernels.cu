@@ -11,7 +11,7 @@
 #define CTB_EXP_LIB
 #include "kin_kernels.h"
 #include "rates_thread.cuh"
-#include "rates_tile.cuh"
+#include "jac_tile.cuh"
 
 #include <algorithm>
 #include <cstdlib>
@@ -151,13 +151,11 @@ __global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const
     Tile t;
     t.tp = smem;
     t.cS = c + s; t.uS = u + s; t.vS = v + s; t.qS = q + s;
-    const unsigned char* spTab = smem + tv.o_sp;
     if (tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
     volatile int* safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
     if (tid == 0) *safeFlag = 0;
     const int barId = 1 + ti;
     const long long nTiles = (a.N + CTB_TS - 1) / CTB_TS;
-    const bool needLogP = tv.hasPdep != 0;
     for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
         const long long n0 = tile * CTB_TS;
         const int nvalid = (int) min((long long) CTB_TS, a.N - n0);
@@ -169,44 +167,11 @@ __global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const
             c[k * CTB_LDC + si] = a.Y[(n0 + sn) * a.ldY + k];
         }
         const long long n = n0 + min(s, nvalid - 1);
+        const double Tn = a.T[n], Pn = a.P[n];
+        tileSync(barId, TT);
         TileScalars sc;
-        sc.T = a.T[n];
-        const double P = a.P[n];
-        tileSync(barId, TT);
-        // ---- Phase::setMassFractions (Phase.cpp:342-360): clip, normalise
-        double sum = 0.0;
-        for (int k = j; k < K; k += NL) {
-            double y = t.cS[k * CTB_LDC];
-            y = y > 0.0 ? y : 0.0;
-            t.cS[k * CTB_LDC] = y;
-            sum += y;
-        }
-        red[j * CTB_TS + s] = sum;
-        tileSync(barId, TT);
-        sum = 0.0;
-#pragma unroll
-        for (int l = 0; l < NL; l++) sum += red[l * CTB_TS + s];
-        const double invSum = 1.0 / sum;
-        sc.logT = log(sc.T);
-        sc.recipT = 1.0 / sc.T;
-        double sym = 0.0;
-        for (int k = j; k < K; k += NL) {
-            const double rmw = reinterpret_cast<const double*>(spTab + (size_t) k * sizeof(Sp2))[15];
-            const double ym = (t.cS[k * CTB_LDC] * invSum) * rmw;
-            t.cS[k * CTB_LDC] = ym;
-            sym += ym;
-        }
-        red[(NL + j) * CTB_TS + s] = sym;
-        tileSync(barId, TT);
-        sym = 0.0;
-#pragma unroll
-        for (int l = 0; l < NL; l++) sym += red[(NL + l) * CTB_TS + s];
-        // setState_TP -> IdealGasPhase::setPressure (IdealGasPhase.h:352-354), molarDensity (Phase.cpp:597-600)
-        const double mmw = 1.0 / sym;
-        const double dens = P * mmw / (sc.T * CTB_GAS_CONSTANT);
-        sc.ctot = dens / mmw;
-        sc.P = CTB_GAS_CONSTANT * sc.ctot * sc.T;
-        sc.logP = needLogP ? log(sc.P) : 0.0;
+        double dens;
+        kinStateTile<NL, TT>(tv, t, red, barId, s, j, Tn, Pn, sc, dens);
         // ---- concentrations, u = exp(-g'), v = c exp(g')
         double unused = 0.0;
         if (speciesPhaseTile<NL, false>(tv, t, sc, 1.0, dens, j, unused)) *safeFlag = 1;
@@ -229,6 +194,93 @@ __global__ void __launch_bounds__(MAXT) ratesTileKernel(const TileView tv, const
             const int k = i - si * K;
             if (si < nvalid) a.wdot[(n0 + si) * a.ldW + k] = c[k * CTB_LDC + si];
         }
+        tileSync(barId, TT);
+    }
+}
+
+// ---------------------------------------------------------------------------- jacobian, tiles
+
+//! netProductionRates_ddX / _ddCi for tiles of 16 states (jac_tile.cuh), dense column-major K x K per
+//! state. W = 4 warps per tile (8 reaction lanes). Shared memory:
+//!   [tile + Jacobian tables (TMA)] [mbarrier, flags] [per tile: c, u, w rows | q rows / 8 column buffers]
+template <int W, int MAXT>
+__global__ void __launch_bounds__(MAXT) jacTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
+                                                      const JacArgs a, double* __restrict__ scratch, const int tileDoubles,
+                                                      const int tableBytes)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + tableBytes);
+    tmaStage(smem, gblob + tv.begin, tv.bytesJac, bar);
+    constexpr int TT = W * 32, NL = 2 * W;
+    const int ti = threadIdx.x / TT, tid = threadIdx.x % TT;
+    const int tilesPerCta = blockDim.x / TT;
+    const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
+    const int K = tv.K, R = tv.R;
+    double* c = reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles;
+    double* u = c + K * CTB_LDC;
+    double* w = u + K * CTB_LDC;
+    double* q = w + K * CTB_LDC;          // q rows, later the NL private column buffers [K][17]
+    double* red = q;
+    Tile t;
+    t.tp = smem;
+    t.cS = c + s; t.uS = u + s; t.vS = w + s; t.qS = q + s;
+    double* colBuf = q + (size_t) j * K * CTB_LDC;
+    double* colS = colBuf + s;
+    JacRows jr;
+    {
+        double* g = scratch + ((size_t) blockIdx.x * tilesPerCta + ti) * jacScratchDoubles(R, tv.nTb) + s;
+        jr.kfM = g; jr.krM = g + (size_t) R * CTB_TS; jr.h2 = jr.krM + (size_t) R * CTB_TS;
+        jr.we = jr.h2 + (size_t) (R + 1) * CTB_TS;
+        if (j == 0) jr.h2[R * CTB_TS] = 0.0; // the all-zero row of the padded gather entries
+    }
+    volatile int* safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
+    if (tid == 0) *safeFlag = 0;
+    const int barId = 1 + ti;
+    const bool skip3b = a.skipThirdBodies != 0, skipFalloff = a.skipFalloff != 0;
+    const unsigned halfMask = 0xFFFFu << (16 * ((threadIdx.x >> 4) & 1));
+    const int l16 = threadIdx.x & 15;
+    const long long nTiles = (a.N + CTB_TS - 1) / CTB_TS;
+    for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
+        const long long n0 = tile * CTB_TS;
+        const int nvalid = (int) min((long long) CTB_TS, a.N - n0);
+        for (int i = tid; i < CTB_TS * K; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicK);
+            const int k = i - si * K;
+            const int sn = min(si, nvalid - 1);
+            c[k * CTB_LDC + si] = a.Y[(n0 + sn) * a.ldY + k];
+        }
+        const long long n = n0 + min(s, nvalid - 1);
+        const double Tn = a.T[n], Pn = a.P[n];
+        tileSync(barId, TT);
+        TileScalars sc;
+        double dens;
+        kinStateTile<NL, TT>(tv, t, red, barId, s, j, Tn, Pn, sc, dens);
+        double unused = 0.0;
+        if (speciesPhaseTile<NL, false, true>(tv, t, sc, 1.0, dens, j, unused)) *safeFlag = 1;
+        tileSync(barId, TT);
+        const bool safe = *safeFlag != 0;
+        if (safe) {
+            speciesPhaseSafeTile<NL>(tv, t, sc, j);
+            tileSync(barId, TT);
+        }
+        if (tid < CTB_TS) q[R * CTB_TS + tid] = 0.0; // the column buffers of the previous tile covered it
+        for (int e = j; e < R; e += NL) ropJacTile<false>(tv, t, sc, e, safe, skip3b, skipFalloff, 0.0, jr);
+        tileSync(barId, TT);
+        if (tid == 0) *safeFlag = 0;
+        // dense default-efficiency part D_k = sum_e nu_ke we_e default_e into the (dead) w rows
+        gatherPhase2Tile<NL>(tv, t, jr.h2, j, [&](int k, double wdot, double D) { t.vS[k * CTB_LDC] = D; });
+        tileSync(barId, TT); // q rows are dead: the column buffers take their place
+        const double scale = a.ddCi ? 1.0 : sc.ctot; // BulkKinetics.cpp:671-676
+        jacColumnsTile<NL>(tv, t, jr, colS, j, skip3b, [&](int jc) {
+            for (int k = 0; k < K; k++) colS[k * CTB_LDC] = (colS[k * CTB_LDC] + t.vS[k * CTB_LDC]) * scale;
+            __syncwarp(halfMask);
+            // transposed write: for every state of the tile, lanes over the rows k of column jc
+            for (int ss = 0; ss < nvalid; ss++) {
+                double* dst = a.jac + (n0 + ss) * (long long) K * K + (long long) jc * K;
+                for (int k = l16; k < K; k += 16) dst[k] = colBuf[k * CTB_LDC + ss];
+            }
+            __syncwarp(halfMask);
+        });
         tileSync(barId, TT);
     }
 }
@@ -480,10 +532,50 @@ static bool launchJacT(const DeviceMech& m, const JacArgs& a, cudaStream_t strea
     return true;
 }
 
-void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream)
+constexpr int JAC_TILE_W = 4, JAC_TILE_MAXT = 512;
+
+JacTilePlan planJacTile(const DeviceMech& m, long long nStates)
+{
+    JacTilePlan p;
+    const TileView& tv = m.tile;
+    constexpr int NL = 2 * JAC_TILE_W;
+    p.tableBytes = ((size_t) tv.bytesJac + 127) & ~(size_t) 127;
+    const size_t span = std::max(std::max((size_t) (tv.R + 1) * CTB_TS, (size_t) NL * tv.K * CTB_LDC), 2 * (size_t) NL * CTB_TS);
+    p.tileDoubles = (3 * (size_t) tv.K * CTB_LDC + span + 15) & ~(size_t) 15;
+    const size_t fixed = p.tableBytes + 128;
+    const size_t budget = (size_t) m.smemOptIn;
+    if (fixed + p.tileDoubles * 8 > budget) return p;
+    int tiles = (int) ((budget - fixed) / (p.tileDoubles * 8));
+    tiles = std::min(tiles, std::min(15, JAC_TILE_MAXT / (JAC_TILE_W * 32)));
+    const long long nTiles = (nStates + CTB_TS - 1) / CTB_TS;
+    tiles = (int) std::min<long long>(tiles, std::max<long long>(1, (nTiles + m.numSMs - 1) / m.numSMs));
+    p.tiles = tiles;
+    p.smemBytes = fixed + (size_t) tiles * p.tileDoubles * 8;
+    p.grid = (int) std::max<long long>(1, std::min<long long>((nTiles + tiles - 1) / tiles, m.numSMs));
+    p.scratchBytes = (size_t) p.grid * tiles * jacScratchDoubles(tv.R, tv.nTb) * 8;
+    return p;
+}
+
+size_t jacScratchBytes(const DeviceMech& m)
+{
+    return (size_t) m.numSMs * 4 * jacScratchDoubles(m.tile.R, m.tile.nTb) * 8;
+}
+
+void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream, void* scratch)
 {
     if (a.N <= 0) return;
     const MechView& v = m.view;
+    static const bool group = [] { const char* e = std::getenv("CTB_JAC_KERNEL"); return e && std::strcmp(e, "group") == 0; }();
+    if (scratch && !group) {
+        const JacTilePlan tp = planJacTile(m, a.N);
+        if (tp.tiles > 0 && tp.scratchBytes <= jacScratchBytes(m)) {
+            auto kern = jacTileKernel<JAC_TILE_W, JAC_TILE_MAXT>;
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) tp.smemBytes);
+            kern<<<tp.grid, tp.tiles * JAC_TILE_W * 32, tp.smemBytes, stream>>>(m.tile, m.dBlob, a, static_cast<double*>(scratch),
+                                                                               (int) tp.tileDoubles, (int) tp.tableBytes);
+            return;
+        }
+    }
     // small Jacobians: a warp per state, several per CTA; large ones: the CTA per state
     const size_t perWarp = ((size_t) 3 * v.K + 6 * v.R + (size_t) v.K * v.K + 2) * 8;
     const size_t budget = (size_t) m.smemOptIn - 1024 - v.hotBytes - 160;

@@ -50,6 +50,16 @@ struct JacArgs {
 
 //! full = false: wdot only (fast path); full = true: any subset of the outputs.
 void launchRates(const DeviceMech& m, const RatesArgs& a, bool full, cudaStream_t stream);
-void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream);
+//! Launch description of the Jacobian tile kernels; tiles == 0: the mechanism does not fit them.
+struct JacTilePlan {
+    int tiles = 0, grid = 0;
+    size_t smemBytes = 0, tileDoubles = 0, tableBytes = 0, scratchBytes = 0;
+};
+JacTilePlan planJacTile(const DeviceMech& m, long long nStates);
+//! Bytes of global scratch a Jacobian launch may need (per concurrent launch / stream).
+size_t jacScratchBytes(const DeviceMech& m);
+//! scratch: jacScratchBytes() of device memory owned by this launch until it completes (nullptr:
+//! the lane-group kernel of rates.cuh is used).
+void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream, void* scratch);
 
 } // namespace ctb

@@ -450,6 +450,34 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         tv.o_genOrder = tb.put(genOrder);
         tb.finish();
         tv.bytes = (uint32_t) tb.data.size();
+        // Jacobian-only tables
+        tv.o_colPtr = tb.put(gPtr); tv.o_colEnt = tb.put(gEnt);
+        tv.o_tbTPtr = tb.put(tbTPtr); tv.o_tbTRxn = tb.put(tbTRxn); tv.o_tbTEff = tb.put(tbTEff);
+        for (int d = 0; d < 2; d++) {
+            const int NL = 4 << d;
+            std::vector<int> order(K);
+            std::iota(order.begin(), order.end(), 0);
+            auto cost = [&](int k) { return (long long) (gPtr[k + 1] - gPtr[k]) + (tbTPtr[k + 1] - tbTPtr[k]) + 4; };
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b2) { return cost(a) > cost(b2); });
+            std::vector<std::vector<int>> lane(NL);
+            std::vector<long long> load(NL, 0);
+            for (int k : order) {
+                int best = 0;
+                for (int l = 1; l < NL; l++) if (load[l] < load[best]) best = l;
+                lane[best].push_back(k);
+                load[best] += cost(k);
+            }
+            std::vector<uint16_t> colOrder;
+            std::vector<int32_t> lanePtr(NL + 1, 0);
+            for (int l = 0; l < NL; l++) {
+                for (int k : lane[l]) colOrder.push_back((uint16_t) k);
+                lanePtr[l + 1] = (int32_t) colOrder.size();
+            }
+            tv.o_colLane[d] = tb.put(lanePtr);
+            tv.o_colOrder[d] = tb.put(colOrder);
+        }
+        tb.finish();
+        tv.bytesJac = (uint32_t) tb.data.size();
         bl.data.insert(bl.data.end(), tb.data.begin(), tb.data.end());
         bl.finish();
         v.bytes = (uint32_t) bl.data.size();

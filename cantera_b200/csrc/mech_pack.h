@@ -217,6 +217,17 @@ struct TileView {
     uint32_t o_plogPtr, o_plogLogP, o_plogA, o_plogB, o_plogEaR;
     uint32_t o_chebPtr, o_chebDim, o_chebLim, o_chebCoef;
     uint32_t o_genPtr, o_genSp, o_genStoich, o_genOrder;
+    // ---- tables of the Jacobian tile kernel only (jac_tile.cuh), laid out directly after the tables
+    // above: it stages [begin, begin + bytesJac), the other tile kernels only [begin, begin + bytes)
+    uint32_t bytesJac;
+    uint32_t o_colPtr;   // int32[K+1]: species-major (reaction, nu) entries = the items of Jacobian column j
+    uint32_t o_colEnt;   // GatherEnt[]
+    uint32_t o_tbTPtr;   // int32[K+1]: explicit third-body efficiencies transposed (species-major)
+    uint32_t o_tbTRxn;   // uint16[]
+    uint32_t o_tbTEff;   // double[] (eff - default)
+    uint32_t o_colLane[2];  // int32[NL+1] for NL = 4, 8: columns dealt to the lanes, balanced by item count
+    uint32_t o_colOrder[2]; // uint16[K]
+    uint32_t pad1;
 };
 
 struct PackedMech {

@@ -16,7 +16,7 @@
 // with the per-slot integrator memory in HBM. Tens of thousands of reactors are in flight per
 // round, so the chemistry runs at the throughput of the rates kernels.
 #include "bdf_batch.cuh"
-#include "rates_tile.cuh"
+#include "reactor_tile.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -225,6 +225,23 @@ struct RowIO {
     __device__ __forceinline__ double P(long long i) const { return Pv[i]; }
 };
 
+//! Carves one tile's shared-memory areas (layout of planRhsTile).
+template <int NL>
+__device__ __forceinline__ ReactorTileBufs carveReactorTile(const TileView& tv, double* base, unsigned char* smem, int tableBytes,
+                                                            int ti)
+{
+    ReactorTileBufs b;
+    b.c = base;
+    b.u = b.c + tv.K * CTB_LDC;
+    b.v = b.u + tv.K * CTB_LDC;
+    b.q = b.v + tv.K * CTB_LDC;
+    b.red2 = b.q + max((tv.R + 1) * CTB_TS, 3 * NL * CTB_TS);
+    b.Trow = b.red2 + NL * CTB_TS;
+    b.safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
+    b.barId = 1 + ti;
+    return b;
+}
+
 template <int W, int MAXT, class IO>
 __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
                                                            const IO io, const int tileDoubles, const int tableBytes)
@@ -237,21 +254,13 @@ __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, co
     const int tilesPerCta = blockDim.x / TT;
     const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
     const int K = tv.K, R = tv.R, n = K + 1;
-    double* c = reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles;
-    double* u = c + K * CTB_LDC;
-    double* v = u + K * CTB_LDC;
-    double* q = v + K * CTB_LDC;
-    double* red = q;                                   // [3][NL][16]: dead before the q rows are written
-    double* red2 = q + max((R + 1) * CTB_TS, 3 * NL * CTB_TS); // [NL][16] + Trow[16]: live while the q rows are read
-    double* Trow = red2 + NL * CTB_TS;
+    const ReactorTileBufs b = carveReactorTile<NL>(tv, reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles,
+                                                   smem, tableBytes, ti);
     Tile t;
     t.tp = smem;
-    t.cS = c + s; t.uS = u + s; t.vS = v + s; t.qS = q + s;
-    const double* molwt = CTB_TAB(double, smem, tv.o_molwt);
-    volatile int* safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
-    if (tid == 0) *safeFlag = 0;
-    if (tid < CTB_TS) q[R * CTB_TS + tid] = 0.0; // the all-zero row the padded gather entries point to
-    const int barId = 1 + ti;
+    t.cS = b.c + s; t.uS = b.u + s; t.vS = b.v + s; t.qS = b.q + s;
+    if (tid == 0) *b.safeFlag = 0;
+    if (tid < CTB_TS) b.q[R * CTB_TS + tid] = 0.0; // the all-zero row the padded gather entries point to
     const long long S = io.count();
     const long long nTiles = (S + CTB_TS - 1) / CTB_TS;
     for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
@@ -267,77 +276,22 @@ __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, co
             const long long ss = min(sl0 + si, S - 1);
             const bool ok = sl0 + si < S && io.active(ss);
             const double val = ok ? io.y(ss)[e] : (e == 0 ? 1000.0 : 1.0);
-            if (e == 0) Trow[si] = val; else c[(e - 1) * CTB_LDC + si] = val;
+            if (e == 0) b.Trow[si] = val; else b.c[(e - 1) * CTB_LDC + si] = val;
         }
         const double P = valid ? io.P(sl) : 101325.0;
-        if (2 * NL > R && tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
-        tileSync(barId, TT);
+        tileSync(b.barId, TT);
         TileScalars sc;
-        sc.T = Trow[s];
-        // ---- Phase::setMolesNoTruncate (Phase.cpp:550-568): no clipping
-        double totalMoles = 0.0, totalMass = 0.0;
-        for (int k = j; k < K; k += NL) {
-            const double nk = t.cS[k * CTB_LDC];
-            totalMoles += nk;
-            totalMass += nk * molwt[k];
-        }
-        red[j * CTB_TS + s] = totalMoles;
-        red[(NL + j) * CTB_TS + s] = totalMass;
-        tileSync(barId, TT);
-        totalMoles = 0.0; totalMass = 0.0;
-#pragma unroll
-        for (int l = 0; l < NL; l++) { totalMoles += red[l * CTB_TS + s]; totalMass += red[(NL + l) * CTB_TS + s]; }
-        const double mmw = totalMass / totalMoles;
-        const double f2 = 1.0 / (mmw * totalMoles);
-        const double dens = P * mmw / (sc.T * CTB_GAS_CONSTANT);
-        sc.ctot = dens / mmw;
-        sc.P = CTB_GAS_CONSTANT * sc.ctot * sc.T;
-        sc.logT = log(sc.T);
-        sc.recipT = 1.0 / sc.T;
-        sc.logP = tv.hasPdep ? log(sc.P) : 0.0;
-        // c rows hold n_k: ym = n_k W_k f2 is the mass fraction over W_k, i.e. n_k f2 * ... (reactorRhs: ym = y f2)
-        double sumq = 0.0;
-        if (speciesPhaseTile<NL, true>(tv, t, sc, f2, dens, j, sumq)) *safeFlag = 1;
-        red[(2 * NL + j) * CTB_TS + s] = sumq;
-        tileSync(barId, TT);
-        const bool safe = *safeFlag != 0;
-        if (safe) speciesPhaseSafeTile<NL>(tv, t, sc, j);
-        sumq = 0.0;
-#pragma unroll
-        for (int l = 0; l < NL; l++) sumq += red[(2 * NL + l) * CTB_TS + s];
-        tileSync(barId, TT); // every lane has read the scratch (it aliases the q rows)
-        if (2 * NL > R && tid < CTB_TS) q[R * CTB_TS + tid] = 0.0;
-        ropPhaseTile<NL, true, 1>(tv, t, sc, j, safe);
-        tileSync(barId, TT);
-        if (tid == 0) *safeFlag = 0;
-        // ---- ydot: species rows V wdot_k into the c rows, temperature row from sum_k wdot_k h_k
-        const double vol = totalMass / dens;
-        const double cp_mole = CTB_GAS_CONSTANT * (mmw * sumq);
-        const double totalCp = totalMass * (cp_mole / mmw);
-        const double RT = sc.T * CTB_GAS_CONSTANT;
-        double mcpdTdt = 0.0;
-        const unsigned char* spTab = smem + tv.o_sp;
-        gatherPhaseTile<NL>(tv, t, j, [&](int k, double wdot) {
-            double cp, h, sr, rmw;
-            nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
-            mcpdTdt -= wdot * (h * RT) * vol;
-            t.cS[k * CTB_LDC] = wdot * vol;
-        });
-        red2[j * CTB_TS + s] = mcpdTdt;
-        tileSync(barId, TT);
-        if (j == 0) {
-            mcpdTdt = 0.0;
-#pragma unroll
-            for (int l = 0; l < NL; l++) mcpdTdt += red2[l * CTB_TS + s];
-            if (valid) io.f(sl)[0] = mcpdTdt / totalCp;
-        }
+        ReactorTileAux aux;
+        reactorStateTile<NL, TT>(tv, t, b, s, j, b.Trow[s], P, sc, aux);
+        const double Tdot = reactorRhsTile<NL, TT>(tv, t, b, tid, s, j, sc, aux, t.cS);
+        if (j == 0 && valid) io.f(sl)[0] = Tdot;
         for (int i = tid; i < CTB_TS * K; i += TT) {
             const int si = (int) __umulhi((unsigned) i, tv.magicK);
             const int k = i - si * K;
             const long long ss = sl0 + si;
-            if (ss < S && io.active(ss)) io.f(ss)[1 + k] = c[k * CTB_LDC + si];
+            if (ss < S && io.active(ss)) io.f(ss)[1 + k] = b.c[k * CTB_LDC + si];
         }
-        tileSync(barId, TT);
+        tileSync(b.barId, TT);
     }
 }
 
