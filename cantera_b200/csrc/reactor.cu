@@ -156,7 +156,7 @@ void BatchReactorNet::advance(double t)
     if (cap > 0) {
         const long long S = std::min(m_N, cap);
         if (S != m_slots) {
-            m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr));
+            m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr, reactorJacScratchBytes(m_kin->mech())));
             m_slots = S;
         }
         try {

@@ -45,11 +45,13 @@ void launchAdvance(const DeviceMech& m, const ReactorBatch& b, cudaStream_t stre
 // ---- batch-synchronous integrator (reactor_batch.cu)
 //! Byte offsets of the slot-interleaved arrays inside the workspace.
 struct BatchLayout {
-    size_t slots, pc, setupList, counters;
+    size_t slots, pc, setupList, counters, jacScratch;
 };
 //! Upper bound of useful slots on this device (0: the mechanism does not fit the thread kernels).
 long long batchSlotCap(const DeviceMech& m, int neq);
-size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay);
+size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay, size_t jacScratchBytesFor);
+//! Bytes of global scratch the reactor Jacobian tile kernel may use (part of the workspace)
+size_t reactorJacScratchBytes(const DeviceMech& m);
 //! Integrates every reactor of b to b.tout with S slots; synchronous (returns when all reactors are
 //! done). Returns the number of control/rhs/setup rounds.
 long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* workspace, long long S,

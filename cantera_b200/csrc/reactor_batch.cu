@@ -16,7 +16,7 @@
 // with the per-slot integrator memory in HBM. Tens of thousands of reactors are in flight per
 // round, so the chemistry runs at the throughput of the rates kernels.
 #include "bdf_batch.cuh"
-#include "reactor_tile.cuh"
+#include "jac_tile.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -336,6 +336,152 @@ __global__ void __launch_bounds__(512) batchJacKernel(const MechView v, const un
     }
 }
 
+//! The same Jacobian for TILES of 16 flagged slots (jac_tile.cuh): J = d(ydot)/dy of the const-pressure
+//! mole reactor as buildNewtonMatrix of bdf.cuh forms it —
+//!   species block  d(V wdot_k)/d n_j = ddCi_kj + (V wdot_k / (V c_tot) - sum_l ddCi_kl c_l / c_tot)
+//!   T row          -(sum_k h_k J_kj + Tdot cp_j) / (m cp)          (IdealGasConstPressureMoleReactor.cpp:153-173)
+//!   T column       one-sided finite difference, dT = T sqrt(eps)                                 (:126-152)
+//! with the dilution sum taken from the homogeneity of the rates of progress (jac_tile.cuh). W = 4 warps
+//! per tile; shared memory per tile: c, u, w rows | q rows + f(T+dT) rows, later 8 column buffers.
+template <int W, int MAXT>
+__global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
+                                                           const SlotMem mem, double* __restrict__ scratch,
+                                                           const int tileDoubles, const int tableBytes)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + tableBytes);
+    tmaStage(smem, gblob + tv.begin, tv.bytesJac, bar);
+    constexpr int TT = W * 32, NL = 2 * W;
+    const int ti = threadIdx.x / TT, tid = threadIdx.x % TT;
+    const int tilesPerCta = blockDim.x / TT;
+    const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
+    const int K = tv.K, R = tv.R, n = K + 1;
+    double* base = reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles;
+    ReactorTileBufs b;
+    b.c = base;
+    b.u = b.c + K * CTB_LDC;
+    b.v = b.u + K * CTB_LDC;
+    b.q = b.v + K * CTB_LDC;
+    const int qSpan = max((R + 1) * CTB_TS, 3 * NL * CTB_TS);
+    double* fT = b.q + qSpan;  // f(T + dT) rows, flushed before the column buffers take over
+    const int span = max(qSpan + K * CTB_LDC, NL * n * CTB_LDC);
+    b.red2 = b.q + span;
+    b.Trow = b.red2 + NL * CTB_TS;
+    b.safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
+    b.barId = 1 + ti;
+    Tile t;
+    t.tp = smem;
+    t.cS = b.c + s; t.uS = b.u + s; t.vS = b.v + s; t.qS = b.q + s;
+    double* fTS = fT + s;
+    double* colBuf = b.q + (size_t) j * n * CTB_LDC;
+    double* colS = colBuf + s;
+    JacRows jr;
+    {
+        double* g = scratch + ((size_t) blockIdx.x * tilesPerCta + ti) * jacScratchDoubles(R, tv.nTb) + s;
+        jr.kfM = g; jr.krM = g + (size_t) R * CTB_TS; jr.h2 = jr.krM + (size_t) R * CTB_TS;
+        jr.we = jr.h2 + (size_t) (R + 1) * CTB_TS;
+        if (j == 0) jr.h2[R * CTB_TS] = 0.0;
+    }
+    if (tid == 0) *b.safeFlag = 0;
+    const unsigned halfMask = 0xFFFFu << (16 * ((threadIdx.x >> 4) & 1));
+    const int l16 = threadIdx.x & 15;
+    const unsigned char* spTab = smem + tv.o_sp;
+    const int count = mem.setupCount[mem.parity];
+    const int nTiles = (count + CTB_TS - 1) / CTB_TS;
+    for (int tile = blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += gridDim.x * tilesPerCta) {
+        const int e0 = tile * CTB_TS;
+        const int nvalid = min(CTB_TS, count - e0);
+        const int sl = mem.setupList[e0 + min(s, nvalid - 1)];
+        auto loadStates = [&]() {
+            for (int i = tid; i < CTB_TS * n; i += TT) {
+                const int si = (int) __umulhi((unsigned) i, tv.magicN);
+                const int e = i - si * n;
+                const int ss = mem.setupList[e0 + min(si, nvalid - 1)];
+                const double val = (mem.vec(ss) + 8 * n)[e];
+                if (e == 0) b.Trow[si] = val; else b.c[(e - 1) * CTB_LDC + si] = val;
+            }
+        };
+        loadStates();
+        const double P = mem.ctl(sl)->P;
+        if (tid < CTB_TS) b.q[R * CTB_TS + tid] = 0.0; // the column buffers of the previous tile covered it
+        tileSync(b.barId, TT);
+        const double T0 = b.Trow[s];
+        const double dT = T0 * 1.4901161193847656e-08; // sqrt(DBL_EPSILON)
+        TileScalars sc;
+        ReactorTileAux aux;
+        // ---- f(T + dT) into the fT rows
+        reactorStateTile<NL, TT>(tv, t, b, s, j, T0 + dT, P, sc, aux);
+        const double Tdot1 = reactorRhsTile<NL, TT>(tv, t, b, tid, s, j, sc, aux, fTS);
+        // ---- base state: the Jacobian pass
+        loadStates();
+        tileSync(b.barId, TT);
+        reactorStateTile<NL, TT>(tv, t, b, s, j, T0, P, sc, aux);
+        double* red = b.q;
+        double sumq = 0.0;
+        if (speciesPhaseTile<NL, true, true>(tv, t, sc, aux.f2, aux.dens, j, sumq)) *b.safeFlag = 1;
+        red[(2 * NL + j) * CTB_TS + s] = sumq;
+        tileSync(b.barId, TT);
+        const bool safe = *b.safeFlag != 0;
+        if (safe) speciesPhaseSafeTile<NL>(tv, t, sc, j);
+        sumq = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) sumq += red[(2 * NL + l) * CTB_TS + s];
+        tileSync(b.barId, TT);
+        if (3 * NL > R && tid < CTB_TS) b.q[R * CTB_TS + tid] = 0.0;
+        const double rctot = 1.0 / aux.ctot;
+        for (int e = j; e < R; e += NL) ropJacTile<true>(tv, t, sc, e, safe, false, false, rctot, jr);
+        tileSync(b.barId, TT);
+        if (tid == 0) *b.safeFlag = 0;
+        const double cp_mole = CTB_GAS_CONSTANT * (aux.mmw * sumq);
+        aux.totalCp = aux.totalMass * (cp_mole / aux.mmw);
+        const double rN = 1.0 / (aux.vol * aux.ctot), rdT = 1.0 / dT, vol = aux.vol, RT = aux.RT;
+        double mcpdTdt = 0.0;
+        gatherPhase2Tile<NL>(tv, t, jr.h2, j, [&](int k, double wdot, double hsum) {
+            double cp, h, sr, rmw;
+            nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
+            const double f0 = wdot * vol;
+            mcpdTdt -= wdot * (h * RT) * vol;
+            fTS[k * CTB_LDC] = (fTS[k * CTB_LDC] - f0) * rdT; // T column, species rows
+            t.uS[k * CTB_LDC] = h;                            // the (dead) u rows now hold h_k / RT
+            t.vS[k * CTB_LDC] = f0 * rN + hsum;               // the (dead) w rows: what every column gets added
+        });
+        b.red2[j * CTB_TS + s] = mcpdTdt;
+        tileSync(b.barId, TT);
+        mcpdTdt = 0.0;
+#pragma unroll
+        for (int l = 0; l < NL; l++) mcpdTdt += b.red2[l * CTB_TS + s];
+        const double Tdot0 = mcpdTdt / aux.totalCp;
+        if (j == 0) b.Trow[s] = (Tdot1 - Tdot0) * rdT;
+        tileSync(b.barId, TT);
+        // ---- T column of J (column 0 of M): transposed, coalesced
+        for (int i = tid; i < nvalid * n; i += TT) {
+            const int si = (int) __umulhi((unsigned) i, tv.magicN);
+            const int e = i - si * n;
+            mem.M(mem.setupList[e0 + si])[e] = e == 0 ? b.Trow[si] : fT[(e - 1) * CTB_LDC + si];
+        }
+        tileSync(b.barId, TT); // the q and fT rows are dead: the column buffers take their place
+        const double rC = 1.0 / aux.totalCp;
+        jacColumnsTile<NL>(tv, t, jr, colS, j, false, [&](int jc) {
+            double acc = 0.0;
+            for (int k = 0; k < K; k++) {
+                const double val = colS[k * CTB_LDC] + t.vS[k * CTB_LDC];
+                colS[k * CTB_LDC] = val;
+                acc += t.uS[k * CTB_LDC] * val;
+            }
+            double cp, h, sr, rmw;
+            nasaTile(spTab, jc, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
+            colS[K * CTB_LDC] = -(acc * RT + Tdot0 * (CTB_GAS_CONSTANT * cp)) * rC; // T row entry of this column
+            __syncwarp(halfMask);
+            for (int ss = 0; ss < nvalid; ss++) {
+                double* dst = mem.M(mem.setupList[e0 + ss]) + (size_t) (1 + jc) * n;
+                for (int i = l16; i < n; i += 16) dst[i] = colBuf[(i == 0 ? K : i - 1) * CTB_LDC + ss];
+            }
+            __syncwarp(halfMask);
+        });
+        tileSync(b.barId, TT);
+    }
+}
+
 //! (I - gamma J)^-1 of the flagged slots by in-place Gauss-Jordan elimination with partial (row)
 //! pivoting — the role of SUNLinSol_Dense's factorisation (CVodesIntegrator.cpp:382-411), with the
 //! inverse instead of the factors so that the controller's solves have no dependent chain.
@@ -490,8 +636,38 @@ bool launchJacT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
     return true;
 }
 
-void launchJac(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+constexpr int RJAC_TILE_W = 4, RJAC_TILE_MAXT = 512;
+
+//! Launch description of the reactor Jacobian tile kernel (tiles == 0: does not fit).
+JacTilePlan planReactorJacTile(const DeviceMech& m)
 {
+    JacTilePlan p;
+    const TileView& tv = m.tile;
+    constexpr int NL = 2 * RJAC_TILE_W;
+    const int K = tv.K, R = tv.R, n = K + 1;
+    p.tableBytes = ((size_t) tv.bytesJac + 127) & ~(size_t) 127;
+    const size_t qSpan = std::max((size_t) (R + 1) * CTB_TS, 3 * (size_t) NL * CTB_TS);
+    const size_t span = std::max(qSpan + (size_t) K * CTB_LDC, (size_t) NL * n * CTB_LDC);
+    p.tileDoubles = (3 * (size_t) K * CTB_LDC + span + (size_t) NL * CTB_TS + CTB_TS + 15) & ~(size_t) 15;
+    const size_t fixed = p.tableBytes + 128;
+    const size_t budget = (size_t) m.smemOptIn;
+    if (fixed + p.tileDoubles * 8 > budget) return p;
+    int tiles = (int) ((budget - fixed) / (p.tileDoubles * 8));
+    tiles = std::min(tiles, std::min(15, RJAC_TILE_MAXT / (RJAC_TILE_W * 32)));
+    p.tiles = tiles;
+    p.smemBytes = fixed + (size_t) tiles * p.tileDoubles * 8;
+    p.grid = m.numSMs;
+    p.scratchBytes = (size_t) p.grid * tiles * jacScratchDoubles(R, tv.nTb) * 8;
+    return p;
+}
+
+void launchJac(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, const JacTilePlan& tp, void* scratch)
+{
+    if (tp.tiles > 0 && scratch) {
+        batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT><<<tp.grid, tp.tiles * RJAC_TILE_W * 32, tp.smemBytes, stream>>>(
+            m.tile, m.dBlob, mem, static_cast<double*>(scratch), (int) tp.tileDoubles, (int) tp.tableBytes);
+        return;
+    }
     const MechView& v = m.view;
     const size_t groupBytes = (16 + reactorWorkDoubles(v.K, v.R)) * 8;
     const size_t budget = (size_t) m.smemOptIn - 1024 - v.hotBytes - 16;
@@ -544,6 +720,11 @@ bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, co
     return true;
 }
 
+size_t reactorJacScratchBytes(const DeviceMech& m)
+{
+    return (size_t) m.numSMs * 4 * jacScratchDoubles(m.tile.R, m.tile.nTb) * 8;
+}
+
 long long batchSlotCap(const DeviceMech& m, int neq)
 {
     SlotMem tmp = {};
@@ -556,7 +737,7 @@ long long batchSlotCap(const DeviceMech& m, int neq)
     return std::max<long long>(cap, 1);
 }
 
-size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay)
+size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay, size_t jacScratchBytesFor)
 {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t) 255; return o; };
@@ -567,6 +748,7 @@ size_t batchWorkspaceBytes(int neq, long long S, BatchLayout* lay)
     l.pc = take(sizeof(int) * S);
     l.setupList = take(sizeof(int) * S);
     l.counters = take(256);
+    l.jacScratch = take(jacScratchBytesFor ? jacScratchBytesFor : 16);
     if (lay) *lay = l;
     return off;
 }
@@ -576,8 +758,15 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
 {
     const MechView& v = m.view;
     const int n = b.neq;
+    const bool groupJac = std::getenv("CTB_JAC_KERNEL") && std::string(std::getenv("CTB_JAC_KERNEL")) == "group";
+    JacTilePlan jp = groupJac ? JacTilePlan() : planReactorJacTile(m);
+    if (jp.tiles > 0 && jp.scratchBytes > reactorJacScratchBytes(m)) jp = JacTilePlan();
+    if (jp.tiles > 0) {
+        cudaFuncSetAttribute(batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int) jp.smemBytes);
+    }
     BatchLayout l;
-    batchWorkspaceBytes(n, S, &l);
+    batchWorkspaceBytes(n, S, &l, reactorJacScratchBytes(m));
     unsigned char* w = static_cast<unsigned char*>(workspace);
     SlotMem mem = {};
     slotLayout(n, mem);
@@ -641,7 +830,7 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
             batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
         }
         if (e5) cudaEventRecord(e5[2], stream);
-        launchJac(m, mem, stream);
+        launchJac(m, mem, stream, jp, w + l.jacScratch);
         if (e5) cudaEventRecord(e5[3], stream);
         launchInvert(m, mem, stream);
         if (e5) cudaEventRecord(e5[4], stream);
