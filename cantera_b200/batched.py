@@ -293,6 +293,15 @@ class BatchReactorNet:
         clib.check(self._lib.ctb_reactornet_eval(self._h, yd.ctypes.data, yd.size, clib.HOST))
         return yd
 
+    def jacobian(self):
+        """d(ydot)/dy at the current state: [N, K+1, K+1] with out[n, j, i] = d ydot_i / d y_j (host): the
+        reference's ``Reactor.jacobian`` layout transposed per reactor (column-major buffer of
+        ctb_reactornet_getJacobian); includes the exact volume-dilution terms, see include/ctb_clib.h."""
+        n = self.kinetics.n_species + 1
+        J = np.empty((self.n_reactors, n, n))
+        clib.check(self._lib.ctb_reactornet_getJacobian(self._h, J.ctypes.data, J.size, clib.HOST))
+        return J
+
     def last_rounds(self):
         """Kernel rounds of the batch-synchronous integrator in the last advance."""
         return int(clib.check(self._lib.ctb_reactornet_lastRounds(self._h)))

@@ -61,6 +61,7 @@ SIGNATURES = {
     "ctb_reactornet_getState": (_i32, [_i32, _dp, _dp, _i64, _i32]),
     "ctb_reactornet_getStateVector": (_i32, [_i32, _dp, _i64, _i32]),
     "ctb_reactornet_eval": (_i32, [_i32, _dp, _i64, _i32]),
+    "ctb_reactornet_getJacobian": (_i32, [_i32, _dp, _i64, _i32]),
     "ctb_reactornet_lastRounds": (_i32, [_i32]),
     "ctb_reactornet_status": (_i32, [_i32, _i64, C.c_void_p]),
     "ctb_reactornet_solverStats": (_i32, [_i32, _i64, C.c_void_p]),

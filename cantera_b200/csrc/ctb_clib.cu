@@ -356,6 +356,11 @@ int32_t ctb_reactornet_eval(int32_t handle, double* ydot, int64_t bufLen, int32_
     return guard([&] { NetCabinet::at(handle)->eval(ydot, bufLen, memspace); return 0; });
 }
 
+int32_t ctb_reactornet_getJacobian(int32_t handle, double* jac, int64_t bufLen, int32_t memspace)
+{
+    return guard([&] { NetCabinet::at(handle)->jacobian(jac, bufLen, memspace); return 0; });
+}
+
 int32_t ctb_reactornet_status(int32_t handle, int64_t len, int32_t* status)
 {
     return guard([&] { NetCabinet::at(handle)->status(len, status); return 0; });

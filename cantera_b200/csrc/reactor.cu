@@ -236,6 +236,35 @@ void BatchReactorNet::eval(double* ydot, long long bufLen, int memspace)
     }
 }
 
+void BatchReactorNet::jacobian(double* jac, long long bufLen, int memspace)
+{
+    if (!m_haveState) throw CtbError("BatchReactorNet::jacobian", "setState has not been called");
+    const long long per = (long long) m_neq * m_neq, need = m_N * per;
+    if (!jac || bufLen < need) throw CtbError("BatchReactorNet::jacobian", "array size (" + std::to_string(bufLen)
+                                              + ") is too small; needs " + std::to_string(need));
+    if (memspace != CTB_DEVICE && memspace != CTB_HOST) throw CtbError("BatchReactorNet::jacobian", "memspace must be CTB_HOST or CTB_DEVICE");
+    cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
+    cudaStream_t st = m_kin->stream();
+    DevBuf scratch;
+    scratch.reserve(reactorJacScratchBytes(m_kin->mech()));
+    // host memory: chunks of reactors through the staging buffer
+    const long long chunk = memspace == CTB_DEVICE ? m_N : std::max<long long>(16, std::min<long long>(m_N, (256LL << 20) / (8 * per)));
+    if (memspace == CTB_HOST) m_io.reserve(sizeof(double) * (size_t) chunk * per);
+    for (long long n0 = 0; n0 < m_N; n0 += chunk) {
+        const long long n = std::min(chunk, m_N - n0);
+        double* d = memspace == CTB_DEVICE ? jac + n0 * per : m_io.as<double>();
+        if (!launchReactorJacobianTile(m_kin->mech(), n, m_y.as<double>() + n0 * m_neq, m_P.as<double>() + n0, d, scratch.p, st)) {
+            throw CtbError("BatchReactorNet::jacobian", "the mechanism is too large for the Jacobian tile kernel");
+        }
+        cudaCheck(cudaGetLastError(), "jacobian launch");
+        if (memspace == CTB_HOST) {
+            cudaCheck(cudaMemcpyAsync(jac + n0 * per, d, sizeof(double) * n * per, cudaMemcpyDeviceToHost, st), "D2H jac");
+            cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+        }
+    }
+    cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize"); // the scratch goes away with this frame
+}
+
 void BatchReactorNet::status(long long len, int32_t* out)
 {
     if (len < m_N || !out) throw CtbError("BatchReactorNet::status", "array size (" + std::to_string(len)

@@ -68,6 +68,10 @@ void launchReactorEval(const DeviceMech& m, long long N, const double* y, const 
 //! The same through the tile kernel (reactor_batch.cu); false if the mechanism does not fit it
 bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
                            cudaStream_t stream);
+//! J = d(ydot)/dy of every reactor through the Jacobian tile kernel (reactor_batch.cu); scratch:
+//! reactorJacScratchBytes() of device memory. false if the mechanism does not fit the kernel.
+bool launchReactorJacobianTile(const DeviceMech& m, long long N, const double* y, const double* P, double* jac,
+                               void* scratch, cudaStream_t stream);
 //! doubles of integrator memory per reactor
 long long reactorHistDoubles(int neq);
 
@@ -96,6 +100,11 @@ public:
     void getStateVector(double* y, long long bufLen, int memspace);
     //! ReactorNet::eval (ReactorNet.cpp:617-635) at the current state: ydot[n*(K+1) + i]
     void eval(double* ydot, long long bufLen, int memspace);
+    //! The Jacobian d(ydot)/dy of ReactorNet::eval at the current state, dense column-major
+    //! (K+1) x (K+1) per reactor: jac[n*(K+1)^2 + j*(K+1) + i] = d ydot_i / d y_j — the matrix the Newton
+    //! iteration uses (IdealGasConstPressureMoleReactor::getJacobianElements,
+    //! IdealGasConstPressureMoleReactor.cpp:108-174, plus the exact volume-dilution terms).
+    void jacobian(double* jac, long long bufLen, int memspace);
     void status(long long len, int32_t* out);
     void solverStats(long long len, long long* out);
     void setIgnitionMonitor(double dT);

@@ -343,9 +343,30 @@ __global__ void __launch_bounds__(512) batchJacKernel(const MechView v, const un
 //!   T column       one-sided finite difference, dT = T sqrt(eps)                                 (:126-152)
 //! with the dilution sum taken from the homogeneity of the rates of progress (jac_tile.cuh). W = 4 warps
 //! per tile; shared memory per tile: c, u, w rows | q rows + f(T+dT) rows, later 8 column buffers.
-template <int W, int MAXT>
+//! Where the Jacobian tile kernel finds its states and puts its matrices: the flagged slots ...
+struct SlotJacIO {
+    SlotMem mem;
+    __device__ __forceinline__ long long count() const { return mem.setupCount[mem.parity]; }
+    __device__ __forceinline__ const double* y(long long i) const { return mem.vec(mem.setupList[i]) + 8 * mem.n; }
+    __device__ __forceinline__ double P(long long i) const { return mem.ctl(mem.setupList[i])->P; }
+    __device__ __forceinline__ double* M(long long i) const { return mem.M(mem.setupList[i]); }
+};
+//! ... or plain rows (ctb_reactornet_getJacobian)
+struct RowJacIO {
+    long long N;
+    int n;
+    const double* yRows;
+    const double* Pv;
+    double* jac;
+    __device__ __forceinline__ long long count() const { return N; }
+    __device__ __forceinline__ const double* y(long long i) const { return yRows + i * n; }
+    __device__ __forceinline__ double P(long long i) const { return Pv[i]; }
+    __device__ __forceinline__ double* M(long long i) const { return jac + i * (long long) n * n; }
+};
+
+template <int W, int MAXT, class IO>
 __global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, const unsigned char* __restrict__ gblob,
-                                                           const SlotMem mem, double* __restrict__ scratch,
+                                                           const IO io, double* __restrict__ scratch,
                                                            const int tileDoubles, const int tableBytes)
 {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -386,23 +407,21 @@ __global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, co
     const unsigned halfMask = 0xFFFFu << (16 * ((threadIdx.x >> 4) & 1));
     const int l16 = threadIdx.x & 15;
     const unsigned char* spTab = smem + tv.o_sp;
-    const int count = mem.setupCount[mem.parity];
-    const int nTiles = (count + CTB_TS - 1) / CTB_TS;
-    for (int tile = blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += gridDim.x * tilesPerCta) {
-        const int e0 = tile * CTB_TS;
-        const int nvalid = min(CTB_TS, count - e0);
-        const int sl = mem.setupList[e0 + min(s, nvalid - 1)];
+    const long long count = io.count();
+    const long long nTiles = (count + CTB_TS - 1) / CTB_TS;
+    for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
+        const long long e0 = tile * CTB_TS;
+        const int nvalid = (int) min((long long) CTB_TS, count - e0);
         auto loadStates = [&]() {
             for (int i = tid; i < CTB_TS * n; i += TT) {
                 const int si = (int) __umulhi((unsigned) i, tv.magicN);
                 const int e = i - si * n;
-                const int ss = mem.setupList[e0 + min(si, nvalid - 1)];
-                const double val = (mem.vec(ss) + 8 * n)[e];
+                const double val = io.y(e0 + min(si, nvalid - 1))[e];
                 if (e == 0) b.Trow[si] = val; else b.c[(e - 1) * CTB_LDC + si] = val;
             }
         };
         loadStates();
-        const double P = mem.ctl(sl)->P;
+        const double P = io.P(e0 + min(s, nvalid - 1));
         if (tid < CTB_TS) b.q[R * CTB_TS + tid] = 0.0; // the column buffers of the previous tile covered it
         tileSync(b.barId, TT);
         const double T0 = b.Trow[s];
@@ -457,7 +476,7 @@ __global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, co
         for (int i = tid; i < nvalid * n; i += TT) {
             const int si = (int) __umulhi((unsigned) i, tv.magicN);
             const int e = i - si * n;
-            mem.M(mem.setupList[e0 + si])[e] = e == 0 ? b.Trow[si] : fT[(e - 1) * CTB_LDC + si];
+            io.M(e0 + si)[e] = e == 0 ? b.Trow[si] : fT[(e - 1) * CTB_LDC + si];
         }
         tileSync(b.barId, TT); // the q and fT rows are dead: the column buffers take their place
         const double rC = 1.0 / aux.totalCp;
@@ -473,7 +492,7 @@ __global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, co
             colS[K * CTB_LDC] = -(acc * RT + Tdot0 * (CTB_GAS_CONSTANT * cp)) * rC; // T row entry of this column
             __syncwarp(halfMask);
             for (int ss = 0; ss < nvalid; ss++) {
-                double* dst = mem.M(mem.setupList[e0 + ss]) + (size_t) (1 + jc) * n;
+                double* dst = io.M(e0 + ss) + (size_t) (1 + jc) * n;
                 for (int i = l16; i < n; i += 16) dst[i] = colBuf[(i == 0 ? K : i - 1) * CTB_LDC + ss];
             }
             __syncwarp(halfMask);
@@ -618,6 +637,123 @@ RhsTilePlan planRhsTile(const DeviceMech& m, long long S)
     return p;
 }
 
+//! The same inversion with a ROTATING register row: after every pivot step the row is shifted left by
+//! one position (fused into the update: a[j] <- a[j+1] - f b[j]) and the finished inverse column is
+//! appended at the end, so the pivot column is always position 0, no register index depends on the
+//! step, and the step loop is NOT unrolled: ~250 instructions instead of the ~9 000 of the unrolled
+//! kernel, which spent most of its time waiting for instruction fetches (3-4 CTAs per SM walking
+//! through 150 KB of code at different places). One thread per matrix row, CPT >= n columns each.
+template <int RP, int CPT, int MINB>
+__global__ void __launch_bounds__(RP, MINB) batchInvertRotKernel(const SlotMem mem)
+{
+    static_assert(CPT % 2 == 0, "rows are broadcast with 128-bit accesses");
+    __shared__ __align__(16) double colbuf[RP];
+    __shared__ __align__(16) double rowbuf[CPT];
+    __shared__ int piv[CPT];
+    const int n = mem.n;
+    const int row = threadIdx.x, lane = threadIdx.x & 31;
+    const int count = mem.setupCount[mem.parity];
+    const long long tk = mem.prof ? clock64() : 0;
+    for (int e = blockIdx.x; e < count; e += gridDim.x) {
+        const int s = mem.setupList[e];
+        double* Mg = mem.M(s);
+        const double gamma = mem.ctl(s)->gamma;
+        const bool rowOk = row < n;
+        double a[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; j++) {
+            double val = 0.0;
+            if (rowOk && j < n) val = (row == j ? 1.0 : 0.0) - gamma * Mg[(size_t) j * n + row];
+            a[j] = val;
+        }
+        unsigned usedMask = 0;
+#pragma unroll
+        for (int r = 0; r < RP / 32; r++) if (lane + 32 * r >= n) usedMask |= 1u << r;
+        int myStep = -1;
+        bool sing = false;
+        colbuf[row] = a[0];
+        __syncthreads();
+#pragma unroll 1
+        for (int k = 0; k < n; k++) {
+            double best = -1.0;
+            int bi = RP;
+#pragma unroll
+            for (int r = 0; r < RP / 32; r++) {
+                const double val = fabs(colbuf[lane + 32 * r]);
+                if (!((usedMask >> r) & 1u) && val > best) { best = val; bi = lane + 32 * r; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+            }
+            if (!(best > 0.0) || !(best <= 1.7e308)) {
+                sing = true; // zero, NaN or infinite column: the controller retries with a smaller step
+                break;       // uniform: every warp sees the same column
+            }
+            const int p = bi;
+            if ((p & 31) == lane) usedMask |= 1u << (p >> 5);
+            const double f = a[0];
+            const double pinv = 1.0 / colbuf[p];
+            if (row == p) {
+                myStep = k;
+#pragma unroll
+                for (int j = 0; j < CPT - 1; j++) {
+                    a[j] = a[j + 1] * pinv;
+                    rowbuf[j] = a[j];
+                }
+                a[CPT - 1] = pinv;
+                rowbuf[CPT - 1] = pinv;
+                piv[k] = p;
+            }
+            __syncthreads();
+            if (row != p) {
+                const double2* rb = reinterpret_cast<const double2*>(rowbuf);
+#pragma unroll
+                for (int j = 0; j < CPT - 2; j += 2) {
+                    const double2 r2 = rb[j / 2];
+                    a[j] = fma(-f, r2.x, a[j + 1]);
+                    a[j + 1] = fma(-f, r2.y, a[j + 2]);
+                }
+                const double2 r2 = rb[CPT / 2 - 1];
+                a[CPT - 2] = fma(-f, r2.x, a[CPT - 1]);
+                a[CPT - 1] = -f * r2.y;
+            }
+            colbuf[row] = a[0];
+            __syncthreads();
+        }
+        if (!sing) {
+            // positions n .. CPT-1 of the original row are padding: rotate them out
+#pragma unroll 1
+            for (int k = n; k < CPT; k++) {
+#pragma unroll
+                for (int j = 0; j < CPT - 1; j++) a[j] = a[j + 1];
+                a[CPT - 1] = 0.0;
+            }
+            if (myStep >= 0) {
+#pragma unroll
+                for (int j = 0; j < CPT; j++) {
+                    if (j < n) Mg[(size_t) piv[j] * n + myStep] = a[j];
+                }
+            }
+        }
+        if (row == 0) mem.ctl(s)->sing = sing ? 1 : 0;
+        __syncthreads();
+    }
+    if (mem.prof && threadIdx.x == 0) atomicAdd(reinterpret_cast<unsigned long long*>(mem.prof + 5), (unsigned long long) (clock64() - tk));
+}
+
+template <int RP, int CPT, int MINB>
+void launchInvertRotT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
+{
+    auto kern = batchInvertRotKernel<RP, CPT, MINB>;
+    int perSm = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, RP, 0);
+    perSm = std::max(1, perSm);
+    kern<<<m.numSMs * perSm, RP, 0, stream>>>(mem);
+}
+
 template <int NT>
 bool launchJacT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 {
@@ -664,8 +800,8 @@ JacTilePlan planReactorJacTile(const DeviceMech& m)
 void launchJac(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream, const JacTilePlan& tp, void* scratch)
 {
     if (tp.tiles > 0 && scratch) {
-        batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT><<<tp.grid, tp.tiles * RJAC_TILE_W * 32, tp.smemBytes, stream>>>(
-            m.tile, m.dBlob, mem, static_cast<double*>(scratch), (int) tp.tileDoubles, (int) tp.tableBytes);
+        batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT, SlotJacIO><<<tp.grid, tp.tiles * RJAC_TILE_W * 32, tp.smemBytes, stream>>>(
+            m.tile, m.dBlob, SlotJacIO{mem}, static_cast<double*>(scratch), (int) tp.tileDoubles, (int) tp.tableBytes);
         return;
     }
     const MechView& v = m.view;
@@ -697,6 +833,15 @@ void launchInvertT(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 void launchInvert(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 {
     const int n = mem.n;
+    static const bool unrolled = [] { const char* e = std::getenv("CTB_INVERT_KERNEL"); return e && std::string(e) == "unrolled"; }();
+    if (!unrolled && n <= 104) {
+        if (n <= 16) launchInvertRotT<32, 16, 16>(m, mem, stream);
+        else if (n <= 32) launchInvertRotT<32, 32, 12>(m, mem, stream);
+        else if (n <= 56) launchInvertRotT<64, 56, 6>(m, mem, stream);
+        else if (n <= 80) launchInvertRotT<96, 80, 3>(m, mem, stream);
+        else launchInvertRotT<128, 104, 2>(m, mem, stream);
+        return;
+    }
     if (n <= 16) launchInvertT<32, 1, 16>(m, mem, stream);
     else if (n <= 32) launchInvertT<32, 1, 32>(m, mem, stream);
     else if (n <= 56) launchInvertT<64, 1, 56>(m, mem, stream);
@@ -707,6 +852,20 @@ void launchInvert(const DeviceMech& m, const SlotMem& mem, cudaStream_t stream)
 }
 
 } // namespace
+
+bool launchReactorJacobianTile(const DeviceMech& m, long long N, const double* y, const double* P, double* jac,
+                               void* scratch, cudaStream_t stream)
+{
+    if (N <= 0) return true;
+    const JacTilePlan tp = planReactorJacTile(m);
+    if (tp.tiles == 0 || tp.scratchBytes > reactorJacScratchBytes(m)) return false;
+    auto kern = batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT, RowJacIO>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) tp.smemBytes);
+    RowJacIO io = {N, m.tile.K + 1, y, P, jac};
+    kern<<<tp.grid, tp.tiles * RJAC_TILE_W * 32, tp.smemBytes, stream>>>(m.tile, m.dBlob, io, static_cast<double*>(scratch),
+                                                                        (int) tp.tileDoubles, (int) tp.tableBytes);
+    return true;
+}
 
 bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
                            cudaStream_t stream)
@@ -762,8 +921,8 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     JacTilePlan jp = groupJac ? JacTilePlan() : planReactorJacTile(m);
     if (jp.tiles > 0 && jp.scratchBytes > reactorJacScratchBytes(m)) jp = JacTilePlan();
     if (jp.tiles > 0) {
-        cudaFuncSetAttribute(batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int) jp.smemBytes);
+        cudaFuncSetAttribute(batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT, SlotJacIO>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int) jp.smemBytes);
     }
     BatchLayout l;
     batchWorkspaceBytes(n, S, &l, reactorJacScratchBytes(m));

@@ -221,6 +221,16 @@ int32_t ctb_reactornet_getStateVector(int32_t handle, double* y, int64_t bufLen,
 /* ReactorNet::eval (ReactorNet.cpp:617-635; IdealGasConstPressureMoleReactor::eval
  * IdealGasConstPressureMoleReactor.cpp:52-106) at the current solution vectors: ydot, same layout. */
 int32_t ctb_reactornet_eval(int32_t handle, double* ydot, int64_t bufLen, int32_t memspace);
+/* Reactor::jacobian / IdealGasConstPressureMoleReactor::getJacobianElements
+ * (IdealGasConstPressureMoleReactor.cpp:108-174) at the current solution vectors, dense column-major
+ * (K+1) x (K+1) per reactor: jac[n*(K+1)^2 + j*(K+1) + i] = d ydot_i / d y_j, y = [T, n_1..n_K].
+ * This is the matrix the batched Newton iteration uses. It differs from the reference's semi-analytic
+ * preconditioner template in two documented ways: the species block carries the exact
+ * volume-dilution terms (d(V wdot_k)/d n_j = ddCi_kj + wdot_k / c_tot - sum_l ddCi_kl X_l; the reference
+ * keeps ddCi_kj only, :114-123) and the falloff [M]-derivative is analytic instead of a finite
+ * difference (MultiRate.h:135-165). T column: one-sided difference with dT = T sqrt(eps) as :126-152;
+ * T row as :153-173 on this species block. bufLen >= nReactors*(K+1)^2. */
+int32_t ctb_reactornet_getJacobian(int32_t handle, double* jac, int64_t bufLen, int32_t memspace);
 /* Per-reactor integrator status: 0 ok, >0 failure code (CTB_STATUS_*). */
 int32_t ctb_reactornet_status(int32_t handle, int64_t len, int32_t* status);
 /* Per-reactor counters, stats[n*CTB_NSTATS + j] (ReactorNet::solverStats,
