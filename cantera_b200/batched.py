@@ -82,12 +82,24 @@ class _Batch:
 class BatchedGasKinetics:
     """Kinetics/BulkKinetics of one ideal-gas mechanism evaluated for N states per call."""
 
-    def __init__(self, mechanism, device=0):
+    def __init__(self, mechanism, device=0, _handle=None):
         self._lib = clib.lib()
-        self._h = clib.check(self._lib.ctb_kin_newFromFile(mechanism_path(mechanism).encode(), device))
+        self._h = _handle if _handle is not None else \
+            clib.check(self._lib.ctb_kin_newFromFile(mechanism_path(mechanism).encode(), device))
         self.device = device
         self.n_species = clib.check(self._lib.ctb_kin_nSpecies(self._h))
         self.n_reactions = clib.check(self._lib.ctb_kin_nReactions(self._h))
+
+    @classmethod
+    def from_yaml(cls, yaml, phase="", device=0, data_dirs=()):
+        """newSolution(yaml, phase) by the reference itself, in this process, through the optional bridge
+        libctb_cantera.so (include/ctb_cantera.h: ctb_kin_new)."""
+        b = clib.bridge()
+        if b is None:
+            raise clib.CtbError("libctb_cantera.so (the reference bridge) is not built; use a .ctbm table file")
+        for d in data_dirs:
+            clib.check(b.ctb_addDataDirectory(str(d).encode()))
+        return cls(yaml, device, _handle=clib.check(b.ctb_kin_new(-1, str(yaml).encode(), phase.encode(), device)))
 
     # ---- lifetime
     def close(self):

@@ -25,6 +25,7 @@ _STATE = [_i32, _i64, _dp, _dp, _dp, _i64]  # handle, nStates, T, P, Y, ldY
 #: every symbol include/ctb_clib.h declares -> (restype, argtypes)
 SIGNATURES = {
     "ctb_getError": (_i32, [_i32, C.c_char_p]),
+    "ctb_setError": (_i32, [C.c_char_p]),
     "ctb_nDevices": (_i32, []),
     "ctb_version": (_i32, [_i32, C.c_char_p]),
     "ctb_fp64PeakTflops": (_f64, [_i32]),
@@ -88,6 +89,30 @@ def lib():
             fn.argtypes = args
         _LIB = L
     return _LIB
+
+
+#: include/ctb_cantera.h — the optional reference bridge (libctb_cantera.so, built where the reference is)
+BRIDGE_PATH = os.path.join(_HERE, "libctb_cantera.so")
+BRIDGE_SIGNATURES = {
+    "ctb_kin_new": (_i32, [_i32, C.c_char_p, C.c_char_p, _i32]),
+    "ctb_kin_newFromSolution": (_i32, [C.c_void_p, _i32]),
+    "ctb_addDataDirectory": (_i32, [C.c_char_p]),
+}
+_BRIDGE = None
+
+
+def bridge():
+    """The reference bridge, or None if it was not built (it needs the reference at build time)."""
+    global _BRIDGE
+    if _BRIDGE is None and os.path.exists(BRIDGE_PATH):
+        lib()  # libctb.so first: the bridge resolves ctb_kin_newFromTables / ctb_setError against it
+        B = C.CDLL(BRIDGE_PATH, mode=C.RTLD_GLOBAL)
+        for name, (res, args) in BRIDGE_SIGNATURES.items():
+            fn = getattr(B, name)
+            fn.restype = res
+            fn.argtypes = args
+        _BRIDGE = B
+    return _BRIDGE
 
 
 def last_error():

@@ -152,6 +152,12 @@ int32_t ctb_nDevices(void)
 
 int32_t ctb_version(int32_t bufLen, char* buf) { return copyString("0.1.0 sm_100a", bufLen, buf); }
 
+int32_t ctb_setError(const char* message)
+{
+    t_lastError = message ? message : "";
+    return 0;
+}
+
 // ---- BatchedGasKinetics --------------------------------------------------------------------
 
 int32_t ctb_kin_newFromTables(const ctb_mech_tables* tables, int32_t device)

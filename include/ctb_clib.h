@@ -110,6 +110,9 @@ typedef struct ctb_mech_tables {
 /* ct_getCanteraError (ct.yaml:46-49): copies the last error of this thread; returns the length
  * needed (including the terminator) when called with (0, NULL). */
 int32_t ctb_getError(int32_t bufLen, char* buf);
+/* Sets this thread's error message (for companion libraries that report through ctb_getError, e.g. the
+ * reference bridge libctb_cantera.so). Returns 0. */
+int32_t ctb_setError(const char* message);
 /* Number of usable CUDA devices, or -1 with an error set. */
 int32_t ctb_nDevices(void);
 /* "0.1.0 sm_100a" style version string; same length convention as ctb_getError. */
@@ -125,6 +128,7 @@ double ctb_fp64PeakTflops(int32_t device);
 /* newKinetics (KineticsFactory.cpp:65-97) for a mechanism already reduced to flat tables.
  * Returns a handle >= 0. */
 int32_t ctb_kin_newFromTables(const ctb_mech_tables* tables, int32_t device);
+/* (ctb_kin_new(yaml, phase): see include/ctb_cantera.h, the optional reference bridge.) */
 /* Same, from a .ctbm table file written by the extractor (oracle/ref_build/ctb_extract). */
 int32_t ctb_kin_newFromFile(const char* ctbmPath, int32_t device);
 int32_t ctb_kin_del(int32_t handle);

@@ -33,6 +33,24 @@ def test_header_symbols_exported(lib):
     assert sorted(clib.SIGNATURES) == names
 
 
+def test_bridge_exports(lib):
+    """libctb_cantera.so (include/ctb_cantera.h), where it was built: every declared symbol is exported,
+    and a bad file name comes back as -1 with the reference's message on the error stack."""
+    from cantera_b200 import clib
+    b = clib.bridge()
+    if b is None:
+        pytest.skip("libctb_cantera.so not built (needs the reference)")
+    hdr = open(os.path.join(ROOT, "include", "ctb_cantera.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = sorted(set(re.findall(r"\b(ctb_[A-Za-z0-9_]+)\s*\(", hdr)))
+    assert names == sorted(clib.BRIDGE_SIGNATURES)
+    for n in names:
+        assert hasattr(b, n), n
+    assert b.ctb_kin_new(-1, b"/nonexistent-mechanism.yaml", b"", 0) == -1
+    assert "nonexistent-mechanism" in clib.last_error()
+    assert b.ctb_kin_new(3, b"gri30.yaml", b"", 0) == -1
+
+
 def test_version_and_string_convention(lib):
     need = lib.ctb_version(0, None)  # (0, NULL) -> required length (test/clib/test_ctkin.cpp:119-123)
     buf = C.create_string_buffer(need)

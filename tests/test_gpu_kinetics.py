@@ -135,6 +135,31 @@ def test_rates_extreme_temperatures(case, Tlo, Thi, kin_cache, oracle_lib):
     assert float(np.max(np.abs(w - o["wdot"])[live] / sc[live])) <= TOL
 
 
+@pytest.mark.parametrize("yaml,phase,case", [("data/gri30.yaml", "gri30", "gri30"), ("testdata/pdep-test.yaml", "gas", "pdep-test")])
+def test_kin_new_in_process(yaml, phase, case, kin_cache):
+    """ctb_kin_new (include/ctb_cantera.h): newSolution() by the reference in this process -> tables ->
+    ctb_kin_newFromTables, against the handle loaded from the .ctbm file: bit-identical outputs."""
+    import os
+    from conftest import ROOT
+    from cantera_b200 import BatchedGasKinetics, clib
+    if clib.bridge() is None:
+        pytest.skip("libctb_cantera.so not built")
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    kin2 = BatchedGasKinetics.from_yaml(os.path.join(ref_dir, yaml), phase, data_dirs=[os.path.join(ref_dir, "data")])
+    kin = kin_cache(case)
+    assert (kin2.n_species, kin2.n_reactions) == (kin.n_species, kin.n_reactions)
+    rng = np.random.default_rng(11)
+    n, K = 777, kin.n_species
+    T = rng.uniform(800, 2500, n)
+    P = 101325.0 * rng.uniform(1, 50, n)
+    Y = rng.uniform(0, 1, (n, K))
+    Y /= Y.sum(axis=1, keepdims=True)
+    assert np.array_equal(kin2.net_production_rates(T, P, Y), kin.net_production_rates(T, P, Y))
+    assert np.array_equal(kin2.forward_rates_of_progress(T, P, Y), kin.forward_rates_of_progress(T, P, Y))
+    assert np.array_equal(kin2.net_production_rates_ddX(T[:50], P[:50], Y[:50]), kin.net_production_rates_ddX(T[:50], P[:50], Y[:50]))
+    kin2.close()
+
+
 def test_multiplier_and_errors(kin_cache, oracle_lib):
     from cantera_b200 import CtbError
     kin = kin_cache("h2o2")
