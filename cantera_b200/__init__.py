@@ -4,3 +4,4 @@ from .batched import BatchedGasKinetics, BatchReactorNet, mechanism_path  # noqa
 from .clib import CtbError  # noqa: F401
 
 __version__ = "0.1.0"
+from .solution_array import BatchedSolutionArray, MultiGpuKinetics, MultiGpuReactorNet  # noqa: F401,E402
