@@ -446,18 +446,12 @@ static bool launchRatesTileT(const DeviceMech& m, const RatesArgs& a, cudaStream
     return true;
 }
 
-//! The wdot-only path: tiles of 16 states. warpsPerTile: 0 = choose.
+//! The wdot-only path: tiles of 16 states, 8 warps (16 reaction lanes) per tile. Measured on gri30
+//! (profiles/r02_wdot_tile_sweep.txt): 4 warps per tile 252 M states/s, 8 warps 266 M; two reactions in
+//! flight per lane change nothing at 8 warps.
 static bool launchRatesTile(const DeviceMech& m, const RatesArgs& a, cudaStream_t stream)
 {
-    static const int forced = [] { const char* e = std::getenv("CTB_TILE_WARPS"); return e ? std::atoi(e) : 0; }();
-    static const int ilp = [] { const char* e = std::getenv("CTB_TILE_ILP"); return e ? std::atoi(e) : 1; }();
-    const int w = forced ? forced : 8;
-    switch (w * 10 + ilp) {
-    case 81: return launchRatesTileT<8, 768, 1>(m, a, stream);
-    case 82: return launchRatesTileT<8, 768, 2>(m, a, stream);
-    case 42: return launchRatesTileT<4, 512, 2>(m, a, stream);
-    default: return launchRatesTileT<4, 512, 1>(m, a, stream);
-    }
+    return launchRatesTileT<8, 768, 1>(m, a, stream);
 }
 
 //! Threads per CTA of the thread-per-state kernels for this mechanism (0: does not fit).

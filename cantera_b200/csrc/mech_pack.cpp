@@ -417,7 +417,9 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         tv.magicN = (uint32_t) ((0x100000000ULL + (unsigned long long) K) / (unsigned long long) (K + 1));
         tv.o_sp = tb.put(sp); tv.o_molwt = tb.put(molwt); tv.o_rx = tb.put(rx); tv.o_runs = tb.put(runs);
         tv.o_gEnt = tb.put(gEnt2); tv.o_gGen = tb.put(gGen2);
-        for (int d = 0; d < CTB_TILE_DEALS; d++) {
+        // the deal for 16 reaction lanes (wdot and right-hand-side kernels) sits in the common part, the
+        // deal for 8 lanes (Jacobian kernels only) in the Jacobian-only tail below
+        auto putDeal = [&](int d) {
             const int NL = 8 << d;
             std::vector<int> order(K);
             std::iota(order.begin(), order.end(), 0);
@@ -439,7 +441,8 @@ PackedMech packMechanism(const ctb_mech_tables& t)
             }
             tv.o_gSp[d] = tb.put(dealt);
             tv.o_gLane[d] = tb.put(lanePtr);
-        }
+        };
+        putDeal(1);
         tv.o_tbDefault = tb.put(tbDefault); tv.o_tbPtr = tb.put(tbPtr); tv.o_tbSp = tb.put(tbSp); tv.o_tbEff = tb.put(tbEff);
         tv.o_fallLow = tb.put(fallLow); tv.o_fallCoef = tb.put(fallCoef); tv.o_auxMult = tb.put(auxMult);
         tv.o_plogPtr = tb.put(plogPtr); tv.o_plogLogP = tb.put(plogLogP); tv.o_plogA = tb.put(plogA);
@@ -451,6 +454,7 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         tb.finish();
         tv.bytes = (uint32_t) tb.data.size();
         // Jacobian-only tables
+        putDeal(0);
         tv.o_colPtr = tb.put(gPtr); tv.o_colEnt = tb.put(gEnt);
         tv.o_tbTPtr = tb.put(tbTPtr); tv.o_tbTRxn = tb.put(tbTRxn); tv.o_tbTEff = tb.put(tbTEff);
         for (int d = 0; d < 2; d++) {

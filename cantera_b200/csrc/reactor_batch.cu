@@ -235,8 +235,13 @@ __device__ __forceinline__ ReactorTileBufs carveReactorTile(const TileView& tv, 
     b.u = b.c + tv.K * CTB_LDC;
     b.v = b.u + tv.K * CTB_LDC;
     b.q = b.v + tv.K * CTB_LDC;
-    b.red2 = b.q + max((tv.R + 1) * CTB_TS, 3 * NL * CTB_TS);
-    b.Trow = b.red2 + NL * CTB_TS;
+    // red2 aliases the u rows (dead once the rates of progress are formed), the tile's temperatures sit
+    // in a q row that the scratch of the mixture sums does not reach (they are consumed long before
+    // the rates of progress are written); small mechanisms get separate areas after the q rows
+    const int qSpan = max((tv.R + 1) * CTB_TS, 3 * NL * CTB_TS);
+    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 1 >= 3 * NL;
+    b.red2 = uFits ? b.u : b.q + qSpan;
+    b.Trow = qFits ? b.q + (tv.R - 1) * CTB_TS : b.q + qSpan + NL * CTB_TS;
     b.safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
     b.barId = 1 + ti;
     return b;
@@ -617,8 +622,9 @@ RhsTilePlan planRhsTile(const DeviceMech& m, long long S)
     const TileView& tv = m.tile;
     constexpr int NL = 2 * RHS_TILE_W;
     p.tableBytes = ((size_t) tv.bytes + 127) & ~(size_t) 127;
+    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 1 >= 3 * NL; // carveReactorTile
     const size_t d = 3 * (size_t) tv.K * CTB_LDC + std::max((size_t) (tv.R + 1) * CTB_TS, 3 * (size_t) NL * CTB_TS)
-                     + (size_t) NL * CTB_TS + CTB_TS;
+                     + (uFits && qFits ? 0 : (size_t) NL * CTB_TS + CTB_TS);
     p.tileDoubles = (d + 15) & ~(size_t) 15;
     const size_t fixed = p.tableBytes + 128;
     const size_t budget = (size_t) m.smemOptIn;
