@@ -208,14 +208,23 @@ class BatchedGasKinetics:
         return self._jac(self._lib.ctb_kin_getNetProductionRates_ddCi, T, P, Y, out)
 
 
-class BatchReactorNet:
-    """N x (IdealGasConstPressureMoleReactor + ReactorNet) advanced together."""
+REACTOR_TYPES = ("IdealGasConstPressureMoleReactor", "IdealGasMoleReactor", "IdealGasReactor",
+                 "IdealGasConstPressureReactor")
 
-    def __init__(self, kinetics, n_reactors):
+
+class BatchReactorNet:
+    """N x (reactor + ReactorNet) advanced together; ``reactor_type`` is one of REACTOR_TYPES (the reference's
+    class names), default IdealGasConstPressureMoleReactor."""
+
+    def __init__(self, kinetics, n_reactors, reactor_type="IdealGasConstPressureMoleReactor"):
         self._lib = clib.lib()
         self.kinetics = kinetics
         self.n_reactors = int(n_reactors)
-        self._h = clib.check(self._lib.ctb_reactornet_new(kinetics.handle, self.n_reactors))
+        if reactor_type not in REACTOR_TYPES:
+            raise clib.CtbError("unknown reactor type '%s'; one of %s" % (reactor_type, ", ".join(REACTOR_TYPES)))
+        self.reactor_type = reactor_type
+        self._h = clib.check(self._lib.ctb_reactornet_newTyped(kinetics.handle, self.n_reactors, REACTOR_TYPES.index(reactor_type)))
+        self.n_equations = clib.check(self._lib.ctb_reactornet_nEquations(self._h))
         self._rtol, self._atol = 1e-9, 1e-15  # ReactorNet.h:483-485
 
     def close(self):
@@ -294,14 +303,14 @@ class BatchReactorNet:
         return T, Y
 
     def get_state_vector(self):
-        """ReactorNet::getState: [N, K+1] rows [T, n_1..n_K] (host)."""
-        y = np.empty((self.n_reactors, self.kinetics.n_species + 1))
+        """ReactorNet::getState: [N, n_equations] rows, layout by reactor model (host)."""
+        y = np.empty((self.n_reactors, self.n_equations))
         clib.check(self._lib.ctb_reactornet_getStateVector(self._h, y.ctypes.data, y.size, clib.HOST))
         return y
 
     def eval(self):
-        """ReactorNet::eval at the current state: ydot [N, K+1] (host)."""
-        yd = np.empty((self.n_reactors, self.kinetics.n_species + 1))
+        """ReactorNet::eval at the current state: ydot [N, n_equations] (host)."""
+        yd = np.empty((self.n_reactors, self.n_equations))
         clib.check(self._lib.ctb_reactornet_eval(self._h, yd.ctypes.data, yd.size, clib.HOST))
         return yd
 

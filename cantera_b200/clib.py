@@ -50,6 +50,8 @@ SIGNATURES = {
     "ctb_kin_getNetProductionRates_ddX": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddCi": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_reactornet_new": (_i32, [_i32, _i64]),
+    "ctb_reactornet_newTyped": (_i32, [_i32, _i64, _i32]),
+    "ctb_reactornet_nEquations": (_i32, [_i32]),
     "ctb_reactornet_del": (_i32, [_i32]),
     "ctb_reactornet_setState": (_i32, [_i32, _dp, _dp, _dp, _i64, _i32]),
     "ctb_reactornet_setRelativeTolerance": (_i32, [_i32, _f64]),

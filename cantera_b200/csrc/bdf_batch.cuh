@@ -77,6 +77,7 @@ struct SlotMem {
     int* nActive;   // slots that are not idle
     long long* prof; // optional cycle counters of the setup kernel phases (CTB_PROFILE), or null
     int S, n;
+    int rtype;      // reactor model (reactor.h)
     int parity;     // round & 1
     CTB_HD unsigned char* block(int s) const { return slots + (size_t) s * slotBytes; }
     CTB_HD BatchCtl* ctl(int s) const { return reinterpret_cast<BatchCtl*>(block(s)); }
@@ -164,7 +165,8 @@ struct BatchBdf {
     CTB_HD double& F(int i) const { return vec[9 * n + i]; }
 
     CTB_HD void setEwt() const {
-        CTB_FOR_OWN(i) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i == 0 ? p.atol : c.atolS));
+        // species rows: c.atolS (MoleReactor::updateDefaultTolerances, MoleReactor.cpp:64-76); T, V, m rows: atol
+        CTB_FOR_OWN(i) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i < p.sIdx ? p.atol : c.atolS));
     }
     CTB_HD void predict() {
         c.tn += c.h;
@@ -557,11 +559,11 @@ struct BatchBdf {
                         const double yi = yg[i];
                         ZN(0, i) = yi;
                         Y(i) = yi;
-                        if (i > 0) moles += yi;
+                        if (i >= p.sIdx) moles += yi;
                     }
-                    // MoleReactor::updateDefaultTolerances (MoleReactor.cpp:64-76)
+                    // MoleReactor::updateDefaultTolerances (MoleReactor.cpp:64-76): mole reactors only
                     moles = g.sum(moles);
-                    c.atolS = (p.atolUser || !(moles > 0.0)) ? p.atol : p.atol * moles;
+                    c.atolS = (p.atolUser || !reactorIsMole(p.type) || !(moles > 0.0)) ? p.atol : p.atol * moles;
                     c.q = 1; c.L = 2; c.qwait = 2; c.qprime = 1;
                     c.nst = 0; c.nstlp = 0; c.nst0 = 0; c.forceSetup = 0;
                     c.etamax = BDF_ETAMX1;
@@ -574,7 +576,7 @@ struct BatchBdf {
                     setEwt();
                     c.tPrev = c.tn;
                     g.sync();
-                    c.TPrev = ZN(0, 0);
+                    c.TPrev = ZN(0, p.tIdx);
                     c.nfe++;
                     c.pc = PC_START_F0;
                     break;
@@ -595,7 +597,7 @@ struct BatchBdf {
                 c.nst0 = c.nst;
                 c.tPrev = c.tn;
                 g.sync();
-                c.TPrev = ZN(0, 0);
+                c.TPrev = ZN(0, p.tIdx);
                 st = X_ADVANCE;
             } else if (st == PC_START_F0) {
                 // cvHin (Bdf::initialStep of bdf.cuh), first part
@@ -884,7 +886,7 @@ struct BatchBdf {
                 const double t2 = c.tq[2];
                 CTB_FOR_OWN(i) AC(i) *= t2;
                 g.sync();
-                const double Tnow = ZN(0, 0);
+                const double Tnow = ZN(0, p.tIdx);
                 if (!(Tnow == Tnow)) {
                     finishStatus = CTB_STATUS_NOT_FINITE;
                     st = X_FINISH;

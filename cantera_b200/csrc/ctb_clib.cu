@@ -292,6 +292,18 @@ int32_t ctb_reactornet_new(int32_t kinHandle, int64_t nReactors)
     });
 }
 
+int32_t ctb_reactornet_newTyped(int32_t kinHandle, int64_t nReactors, int32_t reactorType)
+{
+    return guard([&] {
+        return (int32_t) NetCabinet::add(std::make_shared<BatchReactorNet>(KinCabinet::at(kinHandle), nReactors, reactorType));
+    });
+}
+
+int32_t ctb_reactornet_nEquations(int32_t handle)
+{
+    return guard([&] { return (int32_t) NetCabinet::at(handle)->nEquations(); });
+}
+
 int32_t ctb_reactornet_del(int32_t handle)
 {
     return guard([&] { NetCabinet::del(handle); return 0; });

@@ -9,12 +9,13 @@
 
 namespace ctb {
 
-BatchReactorNet::BatchReactorNet(std::shared_ptr<BatchedGasKinetics> kin, long long nReactors)
-    : m_kin(std::move(kin)), m_N(nReactors)
+BatchReactorNet::BatchReactorNet(std::shared_ptr<BatchedGasKinetics> kin, long long nReactors, int reactorType)
+    : m_kin(std::move(kin)), m_N(nReactors), m_type(reactorType)
 {
     if (!m_kin) throw CtbError("BatchReactorNet", "null kinetics object");
     if (nReactors < 1) throw CtbError("BatchReactorNet", "the number of reactors must be positive");
-    m_neq = m_kin->nSpecies() + 1;
+    if (reactorType < 0 || reactorType > 3) throw CtbError("BatchReactorNet", "unknown reactor type " + std::to_string(reactorType));
+    m_neq = reactorNeq(m_type, m_kin->nSpecies());
     cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
     const size_t N = (size_t) m_N;
     m_y.reserve(sizeof(double) * N * m_neq);
@@ -38,7 +39,7 @@ BatchReactorNet::~BatchReactorNet()
 
 void BatchReactorNet::setState(const double* T, const double* P, const double* Y, long long ldY, int memspace)
 {
-    const int K = m_neq - 1;
+    const int K = m_kin->nSpecies();
     if (!T || !P || !Y) throw CtbError("BatchReactorNet::setState", "null state pointer");
     if (ldY < K) throw CtbError("BatchReactorNet::setState", "ldY is smaller than the number of species");
     cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
@@ -56,7 +57,7 @@ void BatchReactorNet::setState(const double* T, const double* P, const double* Y
     } else if (memspace != CTB_DEVICE) {
         throw CtbError("BatchReactorNet::setState", "memspace must be CTB_HOST or CTB_DEVICE");
     }
-    launchReactorInit(m_kin->mech(), m_N, dT, dP, dY, ld, m_y.as<double>(), m_P.as<double>(),
+    launchReactorInit(m_kin->mech(), m_type, m_N, dT, dP, dY, ld, m_y.as<double>(), m_P.as<double>(),
                       m_T0.as<double>(), st);
     cudaCheck(cudaGetLastError(), "reactorInit launch");
     cudaCheck(cudaMemsetAsync(m_status.p, 0, sizeof(int32_t) * m_N, st), "cudaMemset");
@@ -143,6 +144,7 @@ void BatchReactorNet::advance(double t)
     cudaCheck(cudaMemsetAsync(m_counter.p, 0, sizeof(unsigned long long), st), "cudaMemset");
     ReactorBatch b = {};
     b.N = m_N; b.neq = m_neq;
+    b.type = m_type; b.tIdx = reactorTIdx(m_type); b.sIdx = reactorSIdx(m_type);
     b.y = m_y.as<double>(); b.P = m_P.as<double>(); b.T0 = m_T0.as<double>();
     b.hist = m_hist.as<double>(); b.histStride = reactorHistDoubles(m_neq);
     b.tIgn = m_tIgn.as<double>(); b.status = m_status.as<int32_t>(); b.stats = m_stats.as<long long>();
@@ -153,10 +155,16 @@ void BatchReactorNet::advance(double t)
     // The batch-synchronous integrator (reactor_batch.cu) handles up to 128 equations per reactor;
     // larger mechanisms take the one-kernel shared-memory integrator (reactor_kernels.cu).
     const long long cap = batchSlotCap(m_kin->mech(), m_neq);
+    if (cap <= 0 && m_type != 0) {
+        throw CtbError("BatchReactorNet::advance", "this reactor model needs the batch integrator (at most 128 equations)");
+    }
     if (cap > 0) {
         const long long S = std::min(m_N, cap);
         if (S != m_slots) {
-            m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr, reactorJacScratchBytes(m_kin->mech())));
+            // models without an analytic Jacobian: room for the n + 1 right-hand sides of every slot's difference quotients
+            const size_t extra = m_type == 0 ? reactorJacScratchBytes(m_kin->mech())
+                                             : sizeof(double) * (size_t) S * (m_neq + 1) * m_neq;
+            m_ws.reserve(batchWorkspaceBytes(m_neq, S, nullptr, extra));
             m_slots = S;
         }
         try {
@@ -167,7 +175,7 @@ void BatchReactorNet::advance(double t)
         cudaCheck(cudaGetLastError(), "batch advance");
     } else {
         m_lastRounds = 0;
-        launchAdvance(m_kin->mech(), b, st);
+        launchAdvance(m_kin->mech(), b, st); // one-kernel integrator: IdealGasConstPressureMoleReactor only
         cudaCheck(cudaGetLastError(), "advance launch");
     }
     m_time = t;
@@ -176,21 +184,21 @@ void BatchReactorNet::advance(double t)
 
 void BatchReactorNet::getState(double* T, double* Y, long long ldY, int memspace)
 {
-    const int K = m_neq - 1;
+    const int K = m_kin->nSpecies();
     if (!m_haveState) throw CtbError("BatchReactorNet::getState", "setState has not been called");
     if (!T || !Y) throw CtbError("BatchReactorNet::getState", "null output pointer");
     if (ldY < K) throw CtbError("BatchReactorNet::getState", "ldY is smaller than the number of species");
     cudaCheck(cudaSetDevice(m_kin->device()), "cudaSetDevice");
     cudaStream_t st = m_kin->stream();
     if (memspace == CTB_DEVICE) {
-        launchReactorContents(m_kin->mech(), m_N, m_y.as<double>(), T, Y, ldY, st);
+        launchReactorContents(m_kin->mech(), m_type, m_N, m_y.as<double>(), T, Y, ldY, st);
         cudaCheck(cudaGetLastError(), "reactorContents launch");
         return;
     }
     if (memspace != CTB_HOST) throw CtbError("BatchReactorNet::getState", "memspace must be CTB_HOST or CTB_DEVICE");
     m_io.reserve(sizeof(double) * (size_t) m_N * (K + 2));
     double* d = m_io.as<double>();
-    launchReactorContents(m_kin->mech(), m_N, m_y.as<double>(), d, d + m_N, K, st);
+    launchReactorContents(m_kin->mech(), m_type, m_N, m_y.as<double>(), d, d + m_N, K, st);
     cudaCheck(cudaGetLastError(), "reactorContents launch");
     cudaCheck(cudaMemcpyAsync(T, d, sizeof(double) * m_N, cudaMemcpyDeviceToHost, st), "D2H T");
     cudaCheck(cudaMemcpy2DAsync(Y, sizeof(double) * ldY, d + m_N, sizeof(double) * K, sizeof(double) * K, m_N,
@@ -226,7 +234,8 @@ void BatchReactorNet::eval(double* ydot, long long bufLen, int memspace)
     }
     // the kernel the integrator itself uses (tile form) wherever the mechanism fits it
     const bool groupRhs = std::getenv("CTB_RHS_KERNEL") && std::string(std::getenv("CTB_RHS_KERNEL")) == "group";
-    if (groupRhs || !launchReactorEvalTile(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st)) {
+    if (groupRhs || !launchReactorEvalTile(m_kin->mech(), m_type, m_N, m_y.as<double>(), m_P.as<double>(), d, st)) {
+        if (m_type != 0) throw CtbError("BatchReactorNet::eval", "the mechanism is too large for the tile kernel of this reactor model");
         launchReactorEval(m_kin->mech(), m_N, m_y.as<double>(), m_P.as<double>(), d, st);
     }
     cudaCheck(cudaGetLastError(), "eval launch");
@@ -239,6 +248,7 @@ void BatchReactorNet::eval(double* ydot, long long bufLen, int memspace)
 void BatchReactorNet::jacobian(double* jac, long long bufLen, int memspace)
 {
     if (!m_haveState) throw CtbError("BatchReactorNet::jacobian", "setState has not been called");
+    if (m_type != 0) throw CtbError("BatchReactorNet::jacobian", "only IdealGasConstPressureMoleReactor exports its Jacobian");
     const long long per = (long long) m_neq * m_neq, need = m_N * per;
     if (!jac || bufLen < need) throw CtbError("BatchReactorNet::jacobian", "array size (" + std::to_string(bufLen)
                                               + ") is too small; needs " + std::to_string(need));

@@ -4,6 +4,7 @@
 #pragma once
 
 #include "engine.h"
+#include "reactor_types.h"
 
 #include <memory>
 
@@ -19,7 +20,8 @@ enum StatSlot {
 //! Device-side description of one advance() call; see reactor_kernels.cu.
 struct ReactorBatch {
     long long N;
-    int neq;               // K + 1
+    int neq;               // equations per reactor (reactorNeq)
+    int type, tIdx, sIdx;  // reactor model, temperature row, first species row
     double* y;             // [N * neq] current solution (T, n_1..n_K), row per reactor
     double* P;             // [N] constant pressure of each reactor (ReactorBase.cpp:44)
     double* T0;            // [N] temperature at setState (ignition monitor reference)
@@ -57,16 +59,16 @@ size_t reactorJacScratchBytes(const DeviceMech& m);
 long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* workspace, long long S,
                              cudaStream_t stream);
 //! y <- getState of a reactor holding (T, P, Y) in 1 m^3 (IdealGasConstPressureMoleReactor.cpp:22-30)
-void launchReactorInit(const DeviceMech& m, long long N, const double* T, const double* P, const double* Y,
+void launchReactorInit(const DeviceMech& m, int type, long long N, const double* T, const double* P, const double* Y,
                        long long ldY, double* y, double* Pout, double* T0, cudaStream_t stream);
 //! (T, Y) of the contents (Phase::setMolesNoTruncate -> massFractions)
-void launchReactorContents(const DeviceMech& m, long long N, const double* y, double* T, double* Y,
+void launchReactorContents(const DeviceMech& m, int type, long long N, const double* y, double* T, double* Y,
                            long long ldY, cudaStream_t stream);
 //! ydot = ReactorNet::eval at the current solution vectors
 void launchReactorEval(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
                        cudaStream_t stream);
 //! The same through the tile kernel (reactor_batch.cu); false if the mechanism does not fit it
-bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+bool launchReactorEvalTile(const DeviceMech& m, int type, long long N, const double* y, const double* P, double* ydot,
                            cudaStream_t stream);
 //! J = d(ydot)/dy of every reactor through the Jacobian tile kernel (reactor_batch.cu); scratch:
 //! reactorJacScratchBytes() of device memory. false if the mechanism does not fit the kernel.
@@ -78,7 +80,9 @@ long long reactorHistDoubles(int neq);
 class BatchReactorNet {
 public:
     //! ReactorNet(reactor) x N (ReactorNet.cpp:37-170)
-    BatchReactorNet(std::shared_ptr<BatchedGasKinetics> kin, long long nReactors);
+    BatchReactorNet(std::shared_ptr<BatchedGasKinetics> kin, long long nReactors, int reactorType = 0);
+    int reactorType() const { return m_type; }
+    int nEquations() const { return m_neq; }
     ~BatchReactorNet();
     BatchReactorNet(const BatchReactorNet&) = delete;
 
@@ -114,6 +118,7 @@ private:
     double effectiveAtol() const;
     std::shared_ptr<BatchedGasKinetics> m_kin;
     long long m_N;
+    int m_type = 0;
     int m_neq;
     double m_time = 0.0;
     double m_rtol = 1e-9, m_atol = 1e-15; // ReactorNet.h:483-485

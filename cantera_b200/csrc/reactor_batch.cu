@@ -202,27 +202,67 @@ __global__ void __launch_bounds__(512) batchRhsKernel(const MechView v, const un
 //! 16 slots of the tile working on one reaction / species. IdealGasConstPressureMoleReactor::updateState
 //! + eval (IdealGasConstPressureMoleReactor.cpp:38-106) as in reactorRhs of bdf.cuh.
 //! Shared memory: [tile tables (TMA)] [mbarrier, flags] [per tile: c rows, u rows, v rows, q rows, scratch].
+//! Increment of column `col` in the forward-difference Jacobian of the reactor models without an analytic
+//! one. The right-hand side is a low-degree polynomial in every mole number / mass fraction apart from
+//! the third-body and mean-molecular-weight factors, so a LARGE increment is accurate (relative error
+//! ~ increment / total) and keeps the rounding error of the quotient small where a species is absent:
+//! sqrt(eps) |y| or 1e-7 of the row's natural scale (total moles; 1 for mass fractions), whichever is larger.
+__device__ __forceinline__ double fdIncrement(int type, int n, const double* ys, int col)
+{
+    const int sIdx = reactorSIdx(type);
+    double scale;
+    if (col < sIdx) {
+        scale = fabs(ys[col]);                         // T, V, m rows
+    } else if (reactorIsMole(type)) {
+        scale = 0.0;
+        for (int k = sIdx; k < n; k++) scale += fabs(ys[k]);
+    } else {
+        scale = 1.0;
+    }
+    return fmax(1.4901161193847656e-08 * fabs(ys[col]), 1e-7 * scale);
+}
+
 //! Where the tile kernel finds its states: the integrator's slots ...
 struct SlotIO {
     SlotMem mem;
     __device__ __forceinline__ long long count() const { return mem.S; }
+    __device__ __forceinline__ int type() const { return mem.rtype; }
     __device__ __forceinline__ bool active(long long i) const { return mem.pc[i] != PC_IDLE; }
-    __device__ __forceinline__ const double* y(long long i) const { return mem.vec((int) i) + 8 * mem.n; }
+    __device__ __forceinline__ double yv(long long i, int e) const { return (mem.vec((int) i) + 8 * mem.n)[e]; }
     __device__ __forceinline__ double* f(long long i) const { return mem.vec((int) i) + 9 * mem.n; }
     __device__ __forceinline__ double P(long long i) const { return mem.ctl((int) i)->P; }
 };
-//! ... or plain rows y[N][K+1] (ReactorNet::eval, ctb_reactornet_eval)
+//! ... or plain rows y[N][neq] (ReactorNet::eval, ctb_reactornet_eval) ...
 struct RowIO {
     long long N;
-    int n;
+    int n, rtype;
     const double* yRows;
     const double* Pv;
     double* ydot;
     __device__ __forceinline__ long long count() const { return N; }
+    __device__ __forceinline__ int type() const { return rtype; }
     __device__ __forceinline__ bool active(long long) const { return true; }
-    __device__ __forceinline__ const double* y(long long i) const { return yRows + i * n; }
+    __device__ __forceinline__ double yv(long long i, int e) const { return yRows[i * n + e]; }
     __device__ __forceinline__ double* f(long long i) const { return ydot + i * n; }
     __device__ __forceinline__ double P(long long i) const { return Pv[i]; }
+};
+//! ... or the n + 1 states of a forward-difference Jacobian of every flagged slot: state i = (flagged
+//! slot i / (n + 1), column i % (n + 1)); column n is the unperturbed state. Right-hand sides go to
+//! Fbuf[i][n]; fdJacFinishKernel forms the difference quotients.
+struct FdIO {
+    SlotMem mem;
+    double* Fbuf;
+    __device__ __forceinline__ long long count() const { return (long long) mem.setupCount[mem.parity] * (mem.n + 1); }
+    __device__ __forceinline__ int type() const { return mem.rtype; }
+    __device__ __forceinline__ bool active(long long) const { return true; }
+    __device__ __forceinline__ double yv(long long i, int e) const {
+        const int slot = mem.setupList[i / (mem.n + 1)], col = (int) (i % (mem.n + 1));
+        const double* ys = mem.vec(slot) + 8 * mem.n;
+        const double val = ys[e];
+        return e == col ? val + fdIncrement(mem.rtype, mem.n, ys, col) : val;
+    }
+    __device__ __forceinline__ double* f(long long i) const { return Fbuf + i * mem.n; }
+    __device__ __forceinline__ double P(long long i) const { return mem.ctl(mem.setupList[i / (mem.n + 1)])->P; }
 };
 
 //! Carves one tile's shared-memory areas (layout of planRhsTile).
@@ -239,9 +279,9 @@ __device__ __forceinline__ ReactorTileBufs carveReactorTile(const TileView& tv, 
     // in a q row that the scratch of the mixture sums does not reach (they are consumed long before
     // the rates of progress are written); small mechanisms get separate areas after the q rows
     const int qSpan = max((tv.R + 1) * CTB_TS, 3 * NL * CTB_TS);
-    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 1 >= 3 * NL;
+    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 3 >= 3 * NL;
     b.red2 = uFits ? b.u : b.q + qSpan;
-    b.Trow = qFits ? b.q + (tv.R - 1) * CTB_TS : b.q + qSpan + NL * CTB_TS;
+    b.Trow = qFits ? b.q + (tv.R - 3) * CTB_TS : b.q + qSpan + NL * CTB_TS;
     b.safeFlag = reinterpret_cast<volatile int*>(smem + tableBytes + 16) + ti;
     b.barId = 1 + ti;
     return b;
@@ -258,7 +298,9 @@ __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, co
     const int ti = threadIdx.x / TT, tid = threadIdx.x % TT;
     const int tilesPerCta = blockDim.x / TT;
     const int s = tid & (CTB_TS - 1), j = tid / CTB_TS;
-    const int K = tv.K, R = tv.R, n = K + 1;
+    const int K = tv.K, R = tv.R;
+    const int type = io.type(), sIdx = reactorSIdx(type), tIdx = reactorTIdx(type), n = K + sIdx;
+    const unsigned magicNeq = (unsigned) ((0x100000000ULL + (unsigned long long) n - 1) / (unsigned long long) n);
     const ReactorTileBufs b = carveReactorTile<NL>(tv, reinterpret_cast<double*>(smem + tableBytes + 128) + (size_t) ti * tileDoubles,
                                                    smem, tableBytes, ti);
     Tile t;
@@ -266,6 +308,8 @@ __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, co
     t.cS = b.c + s; t.uS = b.u + s; t.vS = b.v + s; t.qS = b.q + s;
     if (tid == 0) *b.safeFlag = 0;
     if (tid < CTB_TS) b.q[R * CTB_TS + tid] = 0.0; // the all-zero row the padded gather entries point to
+    // rows of the solution vector that are not species: which of [T, V, m] sits where (reactor.h)
+    const int vIdx = type == 1 || type == 2 ? 1 : -1, mIdx = type >= 2 ? 0 : -1;
     const long long S = io.count();
     const long long nTiles = (S + CTB_TS - 1) / CTB_TS;
     for (long long tile = (long long) blockIdx.x * tilesPerCta + ti; tile < nTiles; tile += (long long) gridDim.x * tilesPerCta) {
@@ -274,29 +318,53 @@ __global__ void __launch_bounds__(MAXT) batchRhsTileKernel(const TileView tv, co
         const bool valid = sl0 + s < S && io.active(sl);
         // every warp of the tile holds all 16 slots: the vote is the same in all of them
         if (!__any_sync(0xffffffffu, valid)) continue;
-        // ---- transposed load of the requested states y = [T, n_1..n_K]; idle slots get a benign state
+        // ---- transposed load of the requested solution vectors; idle slots get a benign state
         for (int i = tid; i < CTB_TS * n; i += TT) {
-            const int si = (int) __umulhi((unsigned) i, tv.magicN);
+            const int si = (int) __umulhi((unsigned) i, magicNeq);
             const int e = i - si * n;
             const long long ss = min(sl0 + si, S - 1);
             const bool ok = sl0 + si < S && io.active(ss);
-            const double val = ok ? io.y(ss)[e] : (e == 0 ? 1000.0 : 1.0);
-            if (e == 0) b.Trow[si] = val; else b.c[(e - 1) * CTB_LDC + si] = val;
+            const double val = ok ? io.yv(ss, e) : (e == tIdx ? 1000.0 : 1.0);
+            if (e >= sIdx) b.c[(e - sIdx) * CTB_LDC + si] = val;
+            else b.Trow[(e == tIdx ? 0 : e == vIdx ? 1 : 2) * CTB_TS + si] = val;
         }
         const double P = valid ? io.P(sl) : 101325.0;
         tileSync(b.barId, TT);
         TileScalars sc;
         ReactorTileAux aux;
-        reactorStateTile<NL, TT>(tv, t, b, s, j, b.Trow[s], P, sc, aux);
+        reactorStateTile<NL, TT>(tv, t, b, s, j, type, b.Trow[s], P, vIdx >= 0 ? b.Trow[CTB_TS + s] : 1.0,
+                                 mIdx >= 0 ? b.Trow[2 * CTB_TS + s] : 1.0, sc, aux);
         const double Tdot = reactorRhsTile<NL, TT>(tv, t, b, tid, s, j, sc, aux, t.cS);
-        if (j == 0 && valid) io.f(sl)[0] = Tdot;
+        if (j == 0 && valid) {
+            double* fs = io.f(sl);
+            fs[tIdx] = Tdot;
+            if (vIdx >= 0) fs[vIdx] = 0.0; // closed reactor: no wall motion, no mass flow
+            if (mIdx >= 0) fs[mIdx] = 0.0;
+        }
         for (int i = tid; i < CTB_TS * K; i += TT) {
             const int si = (int) __umulhi((unsigned) i, tv.magicK);
             const int k = i - si * K;
             const long long ss = sl0 + si;
-            if (ss < S && io.active(ss)) io.f(ss)[1 + k] = b.c[k * CTB_LDC + si];
+            if (ss < S && io.active(ss)) io.f(ss)[sIdx + k] = b.c[k * CTB_LDC + si];
         }
         tileSync(b.barId, TT);
+    }
+}
+
+//! Difference quotients of the forward-difference Jacobian: M[slot][col][row] = (F_col - F_base) / increment.
+__global__ void fdJacFinishKernel(const SlotMem mem, const double* __restrict__ Fbuf)
+{
+    const int n = mem.n;
+    const int count = mem.setupCount[mem.parity];
+    for (int e = blockIdx.x; e < count; e += gridDim.x) {
+        const int slot = mem.setupList[e];
+        const double* ys = mem.vec(slot) + 8 * n;
+        const double* F = Fbuf + (size_t) e * (n + 1) * n;
+        double* M = mem.M(slot);
+        for (int i = threadIdx.x; i < n * n; i += blockDim.x) {
+            const int col = i / n, row = i - col * n;
+            M[i] = (F[(size_t) col * n + row] - F[(size_t) n * n + row]) / fdIncrement(mem.rtype, n, ys, col);
+        }
     }
 }
 
@@ -434,12 +502,12 @@ __global__ void __launch_bounds__(MAXT) batchJacTileKernel(const TileView tv, co
         TileScalars sc;
         ReactorTileAux aux;
         // ---- f(T + dT) into the fT rows
-        reactorStateTile<NL, TT>(tv, t, b, s, j, T0 + dT, P, sc, aux);
+        reactorStateTile<NL, TT>(tv, t, b, s, j, 0, T0 + dT, P, 1.0, 1.0, sc, aux);
         const double Tdot1 = reactorRhsTile<NL, TT>(tv, t, b, tid, s, j, sc, aux, fTS);
         // ---- base state: the Jacobian pass
         loadStates();
         tileSync(b.barId, TT);
-        reactorStateTile<NL, TT>(tv, t, b, s, j, T0, P, sc, aux);
+        reactorStateTile<NL, TT>(tv, t, b, s, j, 0, T0, P, 1.0, 1.0, sc, aux);
         double* red = b.q;
         double sumq = 0.0;
         if (speciesPhaseTile<NL, true, true>(tv, t, sc, aux.f2, aux.dens, j, sumq)) *b.safeFlag = 1;
@@ -622,9 +690,9 @@ RhsTilePlan planRhsTile(const DeviceMech& m, long long S)
     const TileView& tv = m.tile;
     constexpr int NL = 2 * RHS_TILE_W;
     p.tableBytes = ((size_t) tv.bytes + 127) & ~(size_t) 127;
-    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 1 >= 3 * NL; // carveReactorTile
+    const bool uFits = tv.K * CTB_LDC >= NL * CTB_TS, qFits = tv.R - 3 >= 3 * NL; // carveReactorTile
     const size_t d = 3 * (size_t) tv.K * CTB_LDC + std::max((size_t) (tv.R + 1) * CTB_TS, 3 * (size_t) NL * CTB_TS)
-                     + (uFits && qFits ? 0 : (size_t) NL * CTB_TS + CTB_TS);
+                     + (uFits && qFits ? 0 : (size_t) NL * CTB_TS + 3 * CTB_TS);
     p.tileDoubles = (d + 15) & ~(size_t) 15;
     const size_t fixed = p.tableBytes + 128;
     const size_t budget = (size_t) m.smemOptIn;
@@ -639,6 +707,8 @@ RhsTilePlan planRhsTile(const DeviceMech& m, long long S)
     cudaFuncSetAttribute(batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, SlotIO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int) p.smemBytes);
     cudaFuncSetAttribute(batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, RowIO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int) p.smemBytes);
+    cudaFuncSetAttribute(batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, FdIO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int) p.smemBytes);
     return p;
 }
@@ -873,13 +943,13 @@ bool launchReactorJacobianTile(const DeviceMech& m, long long N, const double* y
     return true;
 }
 
-bool launchReactorEvalTile(const DeviceMech& m, long long N, const double* y, const double* P, double* ydot,
+bool launchReactorEvalTile(const DeviceMech& m, int type, long long N, const double* y, const double* P, double* ydot,
                            cudaStream_t stream)
 {
     if (N <= 0) return true;
     const RhsTilePlan tp = planRhsTile(m, N);
     if (tp.tiles == 0) return false;
-    RowIO io = {N, m.tile.K + 1, y, P, ydot};
+    RowIO io = {N, reactorNeq(type, m.tile.K), type, y, P, ydot};
     batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, RowIO><<<tp.grid, tp.tiles * RHS_TILE_W * 32, tp.smemBytes, stream>>>(
         m.tile, m.dBlob, io, (int) tp.tileDoubles, (int) tp.tableBytes);
     return true;
@@ -924,17 +994,18 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     const MechView& v = m.view;
     const int n = b.neq;
     const bool groupJac = std::getenv("CTB_JAC_KERNEL") && std::string(std::getenv("CTB_JAC_KERNEL")) == "group";
-    JacTilePlan jp = groupJac ? JacTilePlan() : planReactorJacTile(m);
+    JacTilePlan jp = (groupJac || b.type != 0) ? JacTilePlan() : planReactorJacTile(m);
     if (jp.tiles > 0 && jp.scratchBytes > reactorJacScratchBytes(m)) jp = JacTilePlan();
     if (jp.tiles > 0) {
         cudaFuncSetAttribute(batchJacTileKernel<RJAC_TILE_W, RJAC_TILE_MAXT, SlotJacIO>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int) jp.smemBytes);
     }
     BatchLayout l;
-    batchWorkspaceBytes(n, S, &l, reactorJacScratchBytes(m));
+    batchWorkspaceBytes(n, S, &l, b.type == 0 ? reactorJacScratchBytes(m) : sizeof(double) * (size_t) S * (n + 1) * n);
     unsigned char* w = static_cast<unsigned char*>(workspace);
     SlotMem mem = {};
     slotLayout(n, mem);
+    mem.rtype = b.type;
     mem.slots = w + l.slots;
     mem.pc = reinterpret_cast<int*>(w + l.pc);
     mem.setupList = reinterpret_cast<int*>(w + l.setupList);
@@ -957,7 +1028,8 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     const int rhsGrid = (int) std::max<long long>(1, std::min<long long>((S + rhsGroups - 1) / rhsGroups, m.numSMs));
     // the tile kernel (rates_tile.cuh) wherever the mechanism's tables and one tile fit in shared memory
     const bool groupRhs = std::getenv("CTB_RHS_KERNEL") && std::string(std::getenv("CTB_RHS_KERNEL")) == "group";
-    const RhsTilePlan tp = groupRhs ? RhsTilePlan() : planRhsTile(m, S);
+    const RhsTilePlan tp = (groupRhs && b.type == 0) ? RhsTilePlan() : planRhsTile(m, S);
+    if (b.type != 0 && tp.tiles == 0) throw std::runtime_error("mechanism too large for the tile kernels of this reactor model");
 
     // ---- control kernel: one shared-memory [ctl | vec] buffer per warp
     int ctlWarps = (int) std::min<size_t>(CTB_CTL_WARPS, (budget - 256) / mem.oM);
@@ -995,7 +1067,15 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
             batchRhsKernel<<<rhsGrid, rhsGroups * 8, rhsSmem, stream>>>(v, m.dBlob, mem, rhsGroupDoubles);
         }
         if (e5) cudaEventRecord(e5[2], stream);
-        launchJac(m, mem, stream, jp, w + l.jacScratch);
+        if (b.type == 0) {
+            launchJac(m, mem, stream, jp, w + l.jacScratch);
+        } else {
+            // forward-difference Jacobian through the right-hand-side tile kernel: n + 1 states per flagged slot
+            double* Fbuf = reinterpret_cast<double*>(w + l.jacScratch);
+            batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, FdIO><<<m.numSMs, tp.tiles * RHS_TILE_W * 32, tp.smemBytes, stream>>>(
+                m.tile, m.dBlob, FdIO{mem, Fbuf}, (int) tp.tileDoubles, (int) tp.tableBytes);
+            fdJacFinishKernel<<<m.numSMs * 4, 256, 0, stream>>>(mem, Fbuf);
+        }
         if (e5) cudaEventRecord(e5[3], stream);
         launchInvert(m, mem, stream);
         if (e5) cudaEventRecord(e5[4], stream);

@@ -51,9 +51,9 @@ __global__ void __launch_bounds__(256) evalKernel(const MechView v, const unsign
     }
 }
 
-// One thread per reactor: Phase::setMassFractions (Phase.cpp:342-360) + setState_TP, then
-// IdealGasConstPressureMoleReactor::getState (:22-30) with m_vol = 1 m^3: y = [T, m Y_k / W_k].
-__global__ void reactorInitKernel(const MechView v, const unsigned char* __restrict__ gmech, long long N,
+// One thread per reactor: Phase::setMassFractions (Phase.cpp:342-360) + setState_TP, then getState of
+// the reactor model with m_vol = 1 m^3 (layouts: reactor.h).
+__global__ void reactorInitKernel(const MechView v, const unsigned char* __restrict__ gmech, const int type, long long N,
                                   const double* __restrict__ T, const double* __restrict__ P,
                                   const double* __restrict__ Y, long long ldY, double* __restrict__ y,
                                   double* __restrict__ Pout, double* __restrict__ T0)
@@ -71,27 +71,39 @@ __global__ void reactorInitKernel(const MechView v, const unsigned char* __restr
     const double mmw = 1.0 / sym;
     const double dens = P[r] * mmw / (T[r] * CTB_GAS_CONSTANT);
     const double mass = dens * 1.0;
-    double* yr = y + r * (K + 1);
-    yr[0] = T[r];
-    for (int k = 0; k < K; k++) yr[1 + k] = mass * rmolwt[k] * (fmax(Yr[k], 0.0) * invSum);
+    const int sIdx = reactorSIdx(type);
+    double* yr = y + r * (K + sIdx);
+    yr[reactorTIdx(type)] = T[r];
+    if (type == 1) yr[1] = 1.0;                       // volume
+    if (type == 2) { yr[0] = mass; yr[1] = 1.0; }
+    if (type == 3) yr[0] = mass;
+    for (int k = 0; k < K; k++) {
+        const double yk = fmax(Yr[k], 0.0) * invSum;
+        yr[sIdx + k] = reactorIsMole(type) ? mass * rmolwt[k] * yk : yk;
+    }
     Pout[r] = P[r];
     T0[r] = T[r];
 }
 
-__global__ void reactorContentsKernel(const MechView v, const unsigned char* __restrict__ gmech, long long N,
+__global__ void reactorContentsKernel(const MechView v, const unsigned char* __restrict__ gmech, const int type, long long N,
                                       const double* __restrict__ y, double* __restrict__ T,
                                       double* __restrict__ Y, long long ldY)
 {
     const long long r = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= N) return;
-    const int K = v.K;
+    const int K = v.K, sIdx = reactorSIdx(type);
     const double* molwt = CTB_TAB(double, gmech, v.o_molwt);
-    const double* yr = y + r * (K + 1);
-    double totalMass = 0.0;
-    for (int k = 0; k < K; k++) totalMass += yr[1 + k] * molwt[k];
-    const double f = 1.0 / totalMass;
-    for (int k = 0; k < K; k++) Y[r * ldY + k] = (yr[1 + k] * molwt[k]) * f;
-    T[r] = yr[0];
+    const double* yr = y + r * (K + sIdx);
+    if (reactorIsMole(type)) {
+        double totalMass = 0.0;
+        for (int k = 0; k < K; k++) totalMass += yr[sIdx + k] * molwt[k];
+        const double f = 1.0 / totalMass;
+        for (int k = 0; k < K; k++) Y[r * ldY + k] = (yr[sIdx + k] * molwt[k]) * f;
+    } else {
+        // ThermoPhase::massFractions after setMassFractions_NoNorm: the values as integrated
+        for (int k = 0; k < K; k++) Y[r * ldY + k] = yr[sIdx + k];
+    }
+    T[r] = yr[reactorTIdx(type)];
 }
 
 } // namespace
@@ -133,22 +145,22 @@ void launchReactorEval(const DeviceMech& m, long long N, const double* y, const 
     evalKernel<<<grid, groups * 32, smemBytes, stream>>>(v, m.dBlob, N, y, P, ydot, groupDoubles);
 }
 
-void launchReactorInit(const DeviceMech& m, long long N, const double* T, const double* P, const double* Y,
+void launchReactorInit(const DeviceMech& m, int type, long long N, const double* T, const double* P, const double* Y,
                        long long ldY, double* y, double* Pout, double* T0, cudaStream_t stream)
 {
     if (N <= 0) return;
     const int threads = 128;
-    reactorInitKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, N, T, P, Y, ldY,
-                                                                                      y, Pout, T0);
+    reactorInitKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, type, N, T, P, Y,
+                                                                                      ldY, y, Pout, T0);
 }
 
-void launchReactorContents(const DeviceMech& m, long long N, const double* y, double* T, double* Y, long long ldY,
+void launchReactorContents(const DeviceMech& m, int type, long long N, const double* y, double* T, double* Y, long long ldY,
                            cudaStream_t stream)
 {
     if (N <= 0) return;
     const int threads = 128;
-    reactorContentsKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, N, y, T, Y,
-                                                                                          ldY);
+    reactorContentsKernel<<<(unsigned) ((N + threads - 1) / threads), threads, 0, stream>>>(m.view, m.dBlob, type, N, y, T,
+                                                                                          Y, ldY);
 }
 
 } // namespace ctb

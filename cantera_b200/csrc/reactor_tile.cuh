@@ -5,6 +5,7 @@
 #pragma once
 
 #include "rates_tile.cuh"
+#include "reactor_types.h"
 
 namespace ctb {
 
@@ -15,44 +16,65 @@ struct ReactorTileBufs {
     double* v;    // [K][17]
     double* q;    // [R+1][16], row R = 0; its first 3 NL rows double as scratch before the rop phase
     double* red2; // [NL][16] scratch that is live while the q rows are read
-    double* Trow; // [16] temperatures of the tile
+    double* Trow; // [3][16] temperatures, volumes and masses of the tile's reactors (the last two by model)
     volatile int* safeFlag;
     int barId;
 };
 
 struct ReactorTileAux {
     double vol, totalCp, RT, ctot, dens, mmw, totalMass, f2;
+    int type; // reactor model (reactor.h)
 };
 
-//! Mixture sums of the tile's reactors from the moles in the c rows: fills aux and sc for temperature T.
-//! Two barriers.
+//! Mixture sums of the tile's reactors from the species rows of the solution vectors in the c rows (moles
+//! for the mole reactors: Phase::setMolesNoTruncate, Phase.cpp:550-568; mass fractions as integrated for
+//! the others: setMassFractions_NoNorm): fills aux and sc for temperature T. vol / mass: the V and m rows
+//! of the models that have them. Two barriers.
 template <int NL, int TT>
 __device__ __forceinline__ void reactorStateTile(const TileView& tv, const Tile& t, const ReactorTileBufs& b, const int s,
-                                                 const int j, const double T, const double P, TileScalars& sc,
+                                                 const int j, const int type, const double T, const double P,
+                                                 const double volRow, const double massRow, TileScalars& sc,
                                                  ReactorTileAux& aux)
 {
     const double* molwt = CTB_TAB(double, t.tp, tv.o_molwt);
+    const unsigned char* spTab = t.tp + tv.o_sp;
     double* red = b.q;
-    // Phase::setMolesNoTruncate (Phase.cpp:550-568): no clipping
-    double totalMoles = 0.0, totalMass = 0.0;
+    const bool mole = reactorIsMole(type);
+    double s0 = 0.0, s1 = 0.0; // mole: sum n, sum n W; mass fractions: sum Y / W
     for (int k = j; k < tv.K; k += NL) {
-        const double nk = t.cS[k * CTB_LDC];
-        totalMoles += nk;
-        totalMass += nk * molwt[k];
+        const double xk = t.cS[k * CTB_LDC];
+        if (mole) {
+            s0 += xk;
+            s1 += xk * molwt[k];
+        } else {
+            s0 += xk * reinterpret_cast<const double*>(spTab + (size_t) k * sizeof(Sp2))[15];
+        }
     }
-    red[j * CTB_TS + s] = totalMoles;
-    red[(NL + j) * CTB_TS + s] = totalMass;
+    red[j * CTB_TS + s] = s0;
+    red[(NL + j) * CTB_TS + s] = s1;
     tileSync(b.barId, TT);
-    totalMoles = 0.0; totalMass = 0.0;
+    s0 = 0.0; s1 = 0.0;
 #pragma unroll
-    for (int l = 0; l < NL; l++) { totalMoles += red[l * CTB_TS + s]; totalMass += red[(NL + l) * CTB_TS + s]; }
+    for (int l = 0; l < NL; l++) { s0 += red[l * CTB_TS + s]; s1 += red[(NL + l) * CTB_TS + s]; }
     tileSync(b.barId, TT); // the scratch is re-used by the caller
     sc.T = T;
-    aux.mmw = totalMass / totalMoles;
-    aux.f2 = 1.0 / (aux.mmw * totalMoles);
-    aux.dens = P * aux.mmw / (T * CTB_GAS_CONSTANT);
-    aux.totalMass = totalMass;
-    aux.vol = totalMass / aux.dens;
+    aux.type = type;
+    if (mole) {
+        aux.totalMass = s1;
+        aux.mmw = s1 / s0;
+        aux.f2 = 1.0 / (aux.mmw * s0);
+    } else {
+        aux.totalMass = massRow;
+        aux.mmw = 1.0 / s0;
+        aux.f2 = 1.0; // unused: the species pass multiplies Y_k by 1 / W_k
+    }
+    if (reactorIsConstP(type)) {
+        aux.dens = P * aux.mmw / (T * CTB_GAS_CONSTANT);
+        aux.vol = aux.totalMass / aux.dens;
+    } else {
+        aux.vol = volRow;
+        aux.dens = aux.totalMass / volRow; // setState_TD(T, m / V)
+    }
     aux.ctot = aux.dens / aux.mmw;
     aux.RT = T * CTB_GAS_CONSTANT;
     sc.ctot = aux.ctot;
@@ -73,7 +95,9 @@ __device__ __forceinline__ double reactorRhsTile(const TileView& tv, const Tile&
 {
     double* red = b.q;
     double sumq = 0.0;
-    if (speciesPhaseTile<NL, true>(tv, t, sc, aux.f2, aux.dens, j, sumq)) *b.safeFlag = 1;
+    const bool mole = reactorIsMole(aux.type), constP = reactorIsConstP(aux.type);
+    if (mole ? speciesPhaseTile<NL, true>(tv, t, sc, aux.f2, aux.dens, j, sumq)
+             : speciesPhaseTile<NL, true, false, true>(tv, t, sc, aux.f2, aux.dens, j, sumq)) *b.safeFlag = 1;
     red[(2 * NL + j) * CTB_TS + s] = sumq;
     tileSync(b.barId, TT);
     const bool safe = *b.safeFlag != 0;
@@ -86,16 +110,20 @@ __device__ __forceinline__ double reactorRhsTile(const TileView& tv, const Tile&
     ropPhaseTile<NL, true, 1>(tv, t, sc, j, safe);
     tileSync(b.barId, TT);
     if (tid == 0) *b.safeFlag = 0;
+    // m cp (constant pressure) or m cv = m (cp - R) (constant volume: IdealGasMoleReactor.cpp:112, IdealGasReactor.cpp:113)
     const double cp_mole = CTB_GAS_CONSTANT * (aux.mmw * sumq);
-    aux.totalCp = aux.totalMass * (cp_mole / aux.mmw);
+    aux.totalCp = aux.totalMass * ((constP ? cp_mole : cp_mole - CTB_GAS_CONSTANT) / aux.mmw);
     double mcpdTdt = 0.0;
     const unsigned char* spTab = t.tp + tv.o_sp;
-    const double vol = aux.vol, RT = aux.RT;
+    const double* molwt = CTB_TAB(double, t.tp, tv.o_molwt);
+    const double vol = aux.vol, RT = aux.RT, rmass = 1.0 / aux.totalMass;
     gatherPhaseTile<NL>(tv, t, j, [&](int k, double wdot) {
         double cp, h, sr, rmw;
         nasaTile(spTab, k, sc.T, sc.logT, sc.recipT, cp, h, sr, rmw);
-        mcpdTdt -= wdot * (h * RT) * vol;
-        outS[k * CTB_LDC] = wdot * vol;
+        // partial molar enthalpy h_k, or internal energy u_k = h_k - RT (getPartialMolarIntEnergies_TV)
+        mcpdTdt -= wdot * ((constP ? h : h - 1.0) * RT) * vol;
+        // dn_k/dt = V wdot_k, or dY_k/dt = V wdot_k W_k / m
+        outS[k * CTB_LDC] = mole ? wdot * vol : (wdot * vol * molwt[k]) * rmass;
     });
     b.red2[j * CTB_TS + s] = mcpdTdt;
     tileSync(b.barId, TT);

@@ -196,6 +196,16 @@ int32_t ctb_kin_getNetProductionRates_ddCi(int32_t handle, int64_t nStates, cons
 /* ReactorNet(reactor) for nReactors independent reactors sharing the mechanism of a kinetics
  * handle (ReactorNet.cpp:37-170). Each reactor starts with volume 1 m^3 (ReactorBase::m_vol). */
 int32_t ctb_reactornet_new(int32_t kinHandle, int64_t nReactors);
+/* The same for the other ideal-gas reactor models (reactor_new + ReactorNet, ctreactor.yaml / ReactorFactory):
+ * solution vectors y are  [T, n_k] | [T, V, n_k] | [m, V, T, Y_k] | [m, T, Y_k]  (kmol, m^3, kg). The models
+ * other than the first integrate with a forward-difference Newton matrix (n + 1 right-hand sides per setup). */
+#define CTB_REACTOR_CONST_PRESSURE_MOLE 0 /* IdealGasConstPressureMoleReactor (IdealGasConstPressureMoleReactor.cpp) */
+#define CTB_REACTOR_MOLE                1 /* IdealGasMoleReactor, constant volume (IdealGasMoleReactor.cpp:97-172)   */
+#define CTB_REACTOR_IDEAL_GAS           2 /* IdealGasReactor, constant volume (IdealGasReactor.cpp:38-117)           */
+#define CTB_REACTOR_CONST_PRESSURE      3 /* IdealGasConstPressureReactor (IdealGasConstPressureReactor.cpp:36-106)  */
+int32_t ctb_reactornet_newTyped(int32_t kinHandle, int64_t nReactors, int32_t reactorType);
+/* ReactorNet::neq per reactor: K + 1, K + 2, K + 3, K + 2 for the four models. */
+int32_t ctb_reactornet_nEquations(int32_t handle);
 int32_t ctb_reactornet_del(int32_t handle);
 /* Solution::setState_TPY on every reactor's contents + ReactorNet::setInitialTime(0)
  * (ReactorNet.cpp:172-177): the integrator restarts from these states. */
@@ -220,7 +230,7 @@ double  ctb_reactornet_time(int32_t handle);                              /* Rea
 int32_t ctb_reactornet_getState(int32_t handle, double* T, double* Y, int64_t ldY,
                                 int32_t memspace);
 /* ReactorNet::getState (ReactorNet.cpp:688-695): the solution vectors y[n*(K+1) + i] = [T, n_1..n_K]
- * (kmol) of every reactor. bufLen >= nReactors*(K+1). */
+ * (kmol) of every reactor (layout by reactor model). bufLen >= nReactors*nEquations. */
 int32_t ctb_reactornet_getStateVector(int32_t handle, double* y, int64_t bufLen, int32_t memspace);
 /* ReactorNet::eval (ReactorNet.cpp:617-635; IdealGasConstPressureMoleReactor::eval
  * IdealGasConstPressureMoleReactor.cpp:52-106) at the current solution vectors: ydot, same layout. */

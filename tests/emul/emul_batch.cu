@@ -65,6 +65,7 @@ int main(int argc, char** argv)
     std::vector<long long> stats(N * CTB_NSTATS, 0);
     unsigned long long counter = 0;
     ReactorBatch b = {};
+    b.type = 0; b.tIdx = 0; b.sIdx = 1;
     b.N = N; b.neq = n; b.y = y.data(); b.P = P.data(); b.T0 = T0.data(); b.hist = hist.data();
     b.histStride = histStride; b.tIgn = tIgn.data(); b.status = status.data(); b.stats = stats.data();
     b.counter = &counter; b.t0 = 0.0; b.tout = th[0]; b.rtol = 1e-9; b.atol = 1e-15 * 0.1 /* reactor.cu kDefaultAtolSafety */; b.atolUser = 0;
