@@ -79,6 +79,20 @@ class _Batch:
         return np.empty(shape, dtype=np.float64)
 
 
+#: python name -> (CTB_Q_* id, "R" | "K"): the reference's Python property names (kinetics.pyx)
+QUANTITIES = {}
+for _i, _fam in enumerate(("forward_rate_constants", "forward_rates_of_progress", "reverse_rates_of_progress",
+                           "net_rates_of_progress")):
+    for _j, _d in enumerate(("ddT", "ddP", "ddC")):
+        QUANTITIES["%s_%s" % (_fam, _d)] = (3 * _i + _j, "R")
+for _i, _fam in enumerate(("creation_rates", "destruction_rates", "net_production_rates")):
+    for _j, _d in enumerate(("ddT", "ddP", "ddC")):
+        QUANTITIES["%s_%s" % (_fam, _d)] = (12 + 3 * _i + _j, "K")
+for _i, _nm in enumerate(("delta_gibbs", "delta_enthalpy", "delta_entropy", "delta_standard_gibbs",
+                          "delta_standard_enthalpy", "delta_standard_entropy")):
+    QUANTITIES[_nm] = (21 + _i, "R")
+
+
 class BatchedGasKinetics:
     """Kinetics/BulkKinetics of one ideal-gas mechanism evaluated for N states per call."""
 
@@ -187,6 +201,24 @@ class BatchedGasKinetics:
 
     def equilibrium_constants(self, T, P, Y, out=None):
         return self._reaction(self._lib.ctb_kin_getEquilibriumConstants, T, P, Y, out)
+
+    def quantity(self, name, T, P, Y, out=None):
+        """Any of QUANTITIES (forward_rates_of_progress_ddT, net_production_rates_ddC, delta_gibbs, ...):
+        [N, R] or [N, K] per the reference's getter of that name."""
+        qid, kind = QUANTITIES[name]
+        b = _Batch(T, P, Y, self.n_species)
+        self._on_torch_stream(b)
+        if out is None:
+            out = b.empty(b.N, self.n_reactions if kind == "R" else self.n_species)
+        if b.N:
+            clib.check(self._lib.ctb_kin_getQuantity(self._h, qid, b.N, _ptr(b.T), _ptr(b.P), _ptr(b.Y), b.ldY, _ptr(out),
+                                                     out.shape[1], b.space))
+        return out
+
+    def __getattr__(self, name):
+        if name in QUANTITIES:
+            return lambda T, P, Y, out=None: self.quantity(name, T, P, Y, out)
+        raise AttributeError(name)
 
     def _jac(self, fn, T, P, Y, out):
         b = _Batch(T, P, Y, self.n_species)

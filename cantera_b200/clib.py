@@ -47,6 +47,7 @@ SIGNATURES = {
     "ctb_kin_getNetRatesOfProgress": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getFwdRateConstants": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getEquilibriumConstants": (_i32, _STATE + [_dp, _i64, _i32]),
+    "ctb_kin_getQuantity": (_i32, [_i32, _i32, _i64, _dp, _dp, _dp, _i64, _dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddX": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddCi": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_reactornet_new": (_i32, [_i32, _i64]),

@@ -263,6 +263,15 @@ CTB_REACTION_GETTER(ctb_kin_getNetRatesOfProgress, ropnet)
 CTB_REACTION_GETTER(ctb_kin_getFwdRateConstants, kf)
 CTB_REACTION_GETTER(ctb_kin_getEquilibriumConstants, kc)
 
+int32_t ctb_kin_getQuantity(int32_t handle, int32_t quantity, int64_t nStates, const double* T, const double* P,
+                            const double* Y, int64_t ldY, double* out, int64_t ld, int32_t memspace)
+{
+    return guard([&] {
+        KinCabinet::at(handle)->quantity(quantity, nStates, T, P, Y, ldY, out, ld, memspace);
+        return 0;
+    });
+}
+
 int32_t ctb_kin_getNetProductionRates_ddX(int32_t handle, int64_t nStates, const double* T,
                                           const double* P, const double* Y, int64_t ldY, double* jac,
                                           int64_t bufLen, int32_t memspace)

@@ -1,5 +1,6 @@
 // engine.cu — BatchedGasKinetics host side: table upload, host<->device staging, launches.
 #include "engine.h"
+#include "derivs_kernels.h"
 
 #include <algorithm>
 #include <cstring>
@@ -217,6 +218,63 @@ void BatchedGasKinetics::rates(long long N, const double* T, const double* P, co
         }
     }
     for (int i = 0; i < NSTAGE; i++) cudaCheck(cudaStreamSynchronize(m_copyStream[i]), "cudaStreamSynchronize");
+}
+
+void BatchedGasKinetics::quantity(int what, long long N, const double* T, const double* P, const double* Y, long long ldY,
+                                  double* out, long long ld, int memspace)
+{
+    const int K = nSpecies(), R = nReactions();
+    if (what < 0 || what >= CTB_Q_COUNT) throw CtbError("BatchedGasKinetics::quantity", "unknown quantity " + std::to_string(what));
+    if (N < 0) throw CtbError("BatchedGasKinetics::quantity", "negative number of states");
+    if (N == 0) return;
+    if (!T || !P || !Y || !out) throw CtbError("BatchedGasKinetics::quantity", "null pointer");
+    if (ldY < K) throw CtbError("BatchedGasKinetics::quantity", "ldY is smaller than the number of species");
+    const bool species = what >= CTB_Q_CDOT_DDT && what <= CTB_Q_WDOT_DDC;
+    const int width = species ? K : R;
+    if (ld < width) throw CtbError("BatchedGasKinetics::quantity", "leading dimension " + std::to_string(ld)
+                                   + " is smaller than the row width " + std::to_string(width));
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    DerivArgs a = {};
+    a.rtolDelta = m_rtolDelta; a.skipThirdBodies = m_skip3b; a.skipFalloff = m_skipFalloff;
+    auto slot = [&](DerivArgs& d) -> double** {
+        if (what < CTB_Q_CDOT_DDT) { // reaction quantities: kf, ropf, ropr, ropnet x (T, P, C)
+            double** fam[4] = {d.kf, d.ropf, d.ropr, d.ropnet};
+            return &fam[what / 3][what % 3];
+        }
+        if (species) {
+            double** fam[3] = {d.cdot, d.ddot, d.wdot};
+            return &fam[(what - CTB_Q_CDOT_DDT) / 3][(what - CTB_Q_CDOT_DDT) % 3];
+        }
+        return &d.delta[what - CTB_Q_DELTA_GIBBS];
+    };
+    if (memspace == CTB_DEVICE) {
+        a.N = N; a.T = T; a.P = P; a.Y = Y; a.ldY = ldY; a.ldR = ld; a.ldW = ld;
+        *slot(a) = out;
+        launchDerivs(m_dev, a, stream());
+        cudaCheck(cudaGetLastError(), "derivsKernel launch");
+        return;
+    }
+    if (memspace != CTB_HOST) throw CtbError("BatchedGasKinetics::quantity", "memspace must be CTB_HOST or CTB_DEVICE");
+    const size_t perState = sizeof(double) * (2 + (size_t) K + width);
+    const long long chunk = std::max<long long>(1024, std::min<long long>(N, (long long) ((64u << 20) / perState)));
+    m_stage[0].reserve((size_t) chunk * perState);
+    cudaStream_t st = m_copyStream[0];
+    for (long long n0 = 0; n0 < N; n0 += chunk) {
+        const long long n = std::min(chunk, N - n0);
+        double* d = m_stage[0].as<double>();
+        double* dT = d; d += chunk;
+        double* dP = d; d += chunk;
+        double* dY = d; d += chunk * K;
+        cudaCheck(cudaMemcpyAsync(dT, T + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D T");
+        cudaCheck(cudaMemcpyAsync(dP, P + n0, sizeof(double) * n, cudaMemcpyHostToDevice, st), "H2D P");
+        copyRows(dY, K, Y + n0 * ldY, ldY, K, n, cudaMemcpyHostToDevice, st, "H2D Y");
+        a.N = n; a.T = dT; a.P = dP; a.Y = dY; a.ldY = K; a.ldR = width; a.ldW = width;
+        *slot(a) = d;
+        launchDerivs(m_dev, a, st);
+        cudaCheck(cudaGetLastError(), "derivsKernel launch");
+        copyRows(out + n0 * ld, ld, d, width, width, n, cudaMemcpyDeviceToHost, st, "D2H");
+        cudaCheck(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    }
 }
 
 void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P, const double* Y,

@@ -70,6 +70,11 @@ public:
     void jacobian(long long N, const double* T, const double* P, const double* Y, long long ldY,
                   double* jac, long long bufLen, bool ddCi, int memspace);
 
+    //! One of the remaining getters (CTB_Q_* of include/ctb_clib.h: the _ddT/_ddP/_ddC families and the
+    //! reaction deltas) for N states: out[n*ld + i], width K (species quantities) or R (reaction quantities).
+    void quantity(int what, long long N, const double* T, const double* P, const double* Y, long long ldY,
+                  double* out, long long ld, int memspace);
+
     const DeviceMech& mech() const { return m_dev; }
     const cantera_b200::MechTables& tables() const { return m_tables; }
     int device() const { return m_dev.device; }

@@ -191,6 +191,45 @@ int32_t ctb_kin_getNetProductionRates_ddCi(int32_t handle, int64_t nStates, cons
                                            const double* P, const double* Y, int64_t ldY,
                                            double* jac, int64_t bufLen, int32_t memspace);
 
+/* The remaining Kinetics getters, one entry point: out[n*ld + i] with row width R (reaction quantities)
+ * or K (species quantities). quantity = CTB_Q_*:
+ *   getFwdRateConstants_ddT/_ddP/_ddC, get{Fwd,Rev,Net}RatesOfProgress_ddT/_ddP/_ddC (BulkKinetics.cpp:284-385),
+ *   get{Creation,Destruction,NetProduction}Rates_ddT/_ddP/_ddC (Kinetics.cpp:459-602),
+ *   getDeltaGibbs / Enthalpy / Entropy and getDeltaSSGibbs / SSEnthalpy / SSEntropy (BulkKinetics.cpp:200-257).
+ * Derivative semantics are the reference's (Kinetics.h:600-700): _ddT at constant pressure-independent
+ * concentrations, _ddC with respect to the total molar concentration at constant T and X; finite
+ * differences with rtol-delta where the reference differences (non-Arrhenius rates, 1/Kc). */
+#define CTB_Q_KF_DDT      0
+#define CTB_Q_KF_DDP      1
+#define CTB_Q_KF_DDC      2
+#define CTB_Q_ROPF_DDT    3
+#define CTB_Q_ROPF_DDP    4
+#define CTB_Q_ROPF_DDC    5
+#define CTB_Q_ROPR_DDT    6
+#define CTB_Q_ROPR_DDP    7
+#define CTB_Q_ROPR_DDC    8
+#define CTB_Q_ROPNET_DDT  9
+#define CTB_Q_ROPNET_DDP  10
+#define CTB_Q_ROPNET_DDC  11
+#define CTB_Q_CDOT_DDT    12
+#define CTB_Q_CDOT_DDP    13
+#define CTB_Q_CDOT_DDC    14
+#define CTB_Q_DDOT_DDT    15
+#define CTB_Q_DDOT_DDP    16
+#define CTB_Q_DDOT_DDC    17
+#define CTB_Q_WDOT_DDT    18
+#define CTB_Q_WDOT_DDP    19
+#define CTB_Q_WDOT_DDC    20
+#define CTB_Q_DELTA_GIBBS       21
+#define CTB_Q_DELTA_ENTHALPY    22
+#define CTB_Q_DELTA_ENTROPY     23
+#define CTB_Q_DELTA_SS_GIBBS    24
+#define CTB_Q_DELTA_SS_ENTHALPY 25
+#define CTB_Q_DELTA_SS_ENTROPY  26
+#define CTB_Q_COUNT             27
+int32_t ctb_kin_getQuantity(int32_t handle, int32_t quantity, int64_t nStates, const double* T, const double* P,
+                            const double* Y, int64_t ldY, double* out, int64_t ld, int32_t memspace);
+
 /* ---- BatchReactorNet: N x { IdealGasConstPressureMoleReactor + ReactorNet } --------------- */
 
 /* ReactorNet(reactor) for nReactors independent reactors sharing the mechanism of a kinetics

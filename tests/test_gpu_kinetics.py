@@ -160,6 +160,59 @@ def test_kin_new_in_process(yaml, phase, case, kin_cache):
     kin2.close()
 
 
+DERIV_CASES = ["h2o2", "gri30", "nDodecane", "pdep-test", "sri-falloff", "tsang-falloff", "chemically-activated-reaction",
+               "explicit-third-bodies"]
+
+
+@pytest.mark.parametrize("case", DERIV_CASES)
+def test_derivative_families_and_deltas(case, kin_cache):
+    """f2: the _ddT / _ddP / _ddC families and the reaction deltas against the reference (golden derivs_*).
+    The deltas and every Arrhenius-rate derivative are analytic on both sides: 1e-12 of the row's
+    largest magnitude. Where the reference itself takes a forward difference with rtol-delta = 1e-8
+    (falloff / Plog / Chebyshev rate constants, d(1/Kc)/dT) two implementations agree only to the noise
+    of that difference, ~1e-16 / 1e-8 amplified by the cancellation in the quotient: 2e-5 of the row's
+    largest magnitude (observed up to 6e-6), 2e-4 for the pure difference quotient kf_ddC (observed 5e-5)."""
+    from cantera_b200.batched import QUANTITIES
+    kin = kin_cache(case)
+    kin.set_derivative_settings()
+    g = golden("derivs", case)
+    N, K, R = g["dims"]
+    T, P, Y = g["T"], g["P"], g["Y"].reshape(N, K)
+    names = {"forward_rate_constants": "kf", "forward_rates_of_progress": "ropf", "reverse_rates_of_progress": "ropr",
+             "net_rates_of_progress": "ropnet", "creation_rates": "cdot", "destruction_rates": "ddot",
+             "net_production_rates": "wdot"}
+    gold = {"delta_gibbs": "deltaGibbs", "delta_enthalpy": "deltaEnthalpy", "delta_entropy": "deltaEntropy",
+            "delta_standard_gibbs": "deltaSSGibbs", "delta_standard_enthalpy": "deltaSSEnthalpy",
+            "delta_standard_entropy": "deltaSSEntropy"}
+    for fam, short in names.items():
+        for d in ("ddT", "ddP", "ddC"):
+            gold["%s_%s" % (fam, d)] = "%s_%s" % (short, d)
+    assert sorted(gold) == sorted(QUANTITIES)
+    worst = {}
+    for name, key in gold.items():
+        ref = g[key].reshape(N, -1)
+        out = kin.quantity(name, T, P, Y)
+        assert out.shape == ref.shape, name
+        scale = np.maximum(np.abs(ref).max(axis=1, keepdims=True), 1e-300)
+        err = float(np.max(np.abs(out - ref) / scale))
+        worst[name] = err
+        # forward_rate_constants_ddC is nothing but the [M]-difference quotient of the falloff rates: near
+        # the high-pressure limit the quotient itself is ~1e-3, so its noise is relatively larger
+        tol = 1e-12 if name.startswith("delta") else 2e-4 if name == "forward_rate_constants_ddC" else 2e-5
+        assert err <= tol, (name, err)
+    # reactions with plain Arrhenius rates are analytic on both sides: exact parity of their rows
+    from cantera_b200.ctbm import read_arrays
+    arr = read_arrays(MECHS[case])["rxn_type"] == 0
+    if arr.any():
+        for name in ("forward_rate_constants_ddT", "forward_rates_of_progress_ddT", "forward_rates_of_progress_ddC"):
+            ref = g[gold[name]].reshape(N, R)[:, arr]
+            out = kin.quantity(name, T, P, Y)[:, arr]
+            sc = np.maximum(np.abs(ref).max(axis=1, keepdims=True), 1e-300)
+            assert float(np.max(np.abs(out - ref) / sc)) <= 1e-12, name
+    # the getters are also attributes named like the reference's Python properties
+    assert np.array_equal(kin.net_production_rates_ddT(T, P, Y), kin.quantity("net_production_rates_ddT", T, P, Y))
+
+
 def test_multiplier_and_errors(kin_cache, oracle_lib):
     from cantera_b200 import CtbError
     kin = kin_cache("h2o2")
