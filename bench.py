@@ -336,6 +336,7 @@ def setup():
         dist.init_process_group("nccl", device_id=x.dev)
     from cantera_b200 import clib
     x.fp64_peak = float(clib.lib().ctb_fp64PeakTflops(x.local))
+    x.dmma_peak = float(clib.lib().ctb_fp64DmmaPeakTflops(x.local))
     if not x.fp64_peak > 0:
         x.fp64_peak = FP64_PEAK_TFLOPS_NOMINAL
     x.peaks = measured_peaks()
@@ -458,6 +459,15 @@ def rates_workload(x, args, workload):
     sampler.join()
     e2e_steps = max(1, min(steps, 3))
     e2e_ms = timed_e2e(x, step_e2e, e2e_steps)
+    pageable = None
+    if workload == "wdot":
+        # the same call with ordinary (pageable) numpy arrays: the C ABI accepts them, the copies then run at
+        # the driver's pageable rate (include/ctb_clib.h: callers who care pin their buffers)
+        import numpy as np
+        pT, pP, pY, pout = (np.array(t.numpy()) for t in (hT, hP, hY, hout))
+        pageable_ms = timed_e2e(x, lambda: kin.net_production_rates(pT, pP, pY, out=pout), 2)
+        pageable = n * x.world * 2 / (pageable_ms * 1e-3)
+        del pT, pP, pY, pout
     rec = {
         "metric": metric, "value": n * x.world * steps / (ms * 1e-3), "unit": "states/s", "n_gpus": x.world,
         "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
@@ -465,7 +475,8 @@ def rates_workload(x, args, workload):
         "config": {"workload": desc, "states_per_gpu": n, "mechanism": "%s (%d species, %d reactions)" % (mech, K, m["R"]), "l2": l2},
         "clocks": sampler.result(),
         "e2e": {"value": e2e_units * x.world * e2e_steps / (e2e_ms * 1e-3), "unit": "states/s",
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "states_per_step": e2e_units},
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "states_per_step": e2e_units,
+                "host_memory": "pinned", "pageable_value": pageable},
         "gpu_launches": launches_per_step * steps,
     }
     hbm = x.peaks.get("hbm_gbs")
@@ -488,6 +499,7 @@ def rates_workload(x, args, workload):
                     "peak = measured live by ctb_fp64PeakTflops (register-resident DFMA micro-benchmark; nominal 148 SM x 64 "
                     "DFMA/clk x 2 x 1.965 GHz = %.1f); algorithmic flop/state = %d (SURVEY.md 8(d)); traffic = dram bytes/state "
                     "of the ncu capture in profiles/ x states" % (FP64_PEAK_TFLOPS_NOMINAL, m["flop"]),
+            "fp64_dmma_peak_tflops": x.dmma_peak,
             "hbm": {"achieved_gbs": gbs, "peak_gbs": hbm, "frac": gbs / hbm if hbm else None, "bytes_per_state": bytes_per},
             "kernel_ms": kernel_ms}
     if x.rank == 0 and not args.no_parity:

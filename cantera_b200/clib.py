@@ -29,6 +29,7 @@ SIGNATURES = {
     "ctb_nDevices": (_i32, []),
     "ctb_version": (_i32, [_i32, C.c_char_p]),
     "ctb_fp64PeakTflops": (_f64, [_i32]),
+    "ctb_fp64DmmaPeakTflops": (_f64, [_i32]),
     "ctb_kin_newFromTables": (_i32, [C.c_void_p, _i32]),
     "ctb_kin_newFromFile": (_i32, [C.c_char_p, _i32]),
     "ctb_kin_del": (_i32, [_i32]),

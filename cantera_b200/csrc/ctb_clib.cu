@@ -104,9 +104,62 @@ __global__ void __launch_bounds__(256) dfmaPeakKernel(double* out, int iters, do
     const double r = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
     if (r == 123.456) out[0] = r; // never true: keeps the chains alive
 }
+// The same question for the FP64 tensor-core path: mma.sync m8n8k4 (DMMA), 8 independent accumulator
+// fragments per warp. north_star: "unless ncu shows FP64 DMMA pays for Newton factorisation".
+__global__ void __launch_bounds__(256) dmmaPeakKernel(double* out, int iters, double a, double b)
+{
+    double c[8][2];
+#pragma unroll
+    for (int u = 0; u < 8; u++) { c[u][0] = threadIdx.x + u; c[u][1] = u; }
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                             : "+d"(c[u][0]), "+d"(c[u][1]) : "d"(a), "d"(b));
+            }
+        }
+    }
+    double r = 0.0;
+#pragma unroll
+    for (int u = 0; u < 8; u++) r += c[u][0] + c[u][1];
+    if (r == 123.456) out[0] = r;
+}
 } // namespace
 
 extern "C" {
+
+double ctb_fp64DmmaPeakTflops(int32_t device)
+{
+    return guarded<double>(CTB_DERR, CTB_DERR, [&] {
+        cudaCheck(cudaSetDevice(device), "cudaSetDevice");
+        int sms = 0;
+        cudaCheck(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute");
+        double* d = nullptr;
+        cudaCheck(cudaMalloc(&d, 64), "cudaMalloc");
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        const int iters = 2048, grid = sms * 8, threads = 256;
+        double best = 0.0;
+        for (int rep = 0; rep < 4; rep++) {
+            cudaEventRecord(e0);
+            dmmaPeakKernel<<<grid, threads>>>(d, iters, 1e-3, 1e-3);
+            cudaEventRecord(e1);
+            cudaCheck(cudaEventSynchronize(e1), "dmmaPeakKernel");
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            // one m8n8k4 = 8 * 8 * 4 multiply-adds per warp
+            const double flop = 2.0 * 256.0 * 8 * 4 * (double) iters * (double) grid * (threads / 32);
+            if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaFree(d);
+        return best;
+    });
+}
 
 double ctb_fp64PeakTflops(int32_t device)
 {

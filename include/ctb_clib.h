@@ -122,6 +122,9 @@ int32_t ctb_version(int32_t bufLen, char* buf);
  * denominator of the FP64-bound kernels (MEASURED_PEAKS.json has no FP64 entry).
  * Returns -999.999 with an error set on failure. */
 double ctb_fp64PeakTflops(int32_t device);
+/* The same measurement for the FP64 tensor-core instruction (mma.sync m8n8k4, DMMA): the number that decides
+ * whether a tensor-core Newton factorisation could pay. */
+double ctb_fp64DmmaPeakTflops(int32_t device);
 
 /* ---- BatchedGasKinetics: Kinetics / BulkKinetics for N states ---------------------------- */
 
