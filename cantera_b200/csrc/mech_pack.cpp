@@ -45,6 +45,31 @@ PackedMech packMechanism(const ctb_mech_tables& t)
     const int K = t.n_species, R = t.n_reactions;
     if (K < 1 || K > 65534) throw std::runtime_error("packMechanism: species count out of range");
     if (R < 0 || R > 65534) throw std::runtime_error("packMechanism: reaction count out of range");
+    // the tables come from outside the library: every index becomes a device offset, so check them
+    auto checkCsr = [&](const char* what, const int32_t* ptr, const int32_t* idx, int rows, int bound) {
+        if (!ptr) throw std::runtime_error(std::string("packMechanism: missing table ") + what);
+        if (ptr[0] != 0) throw std::runtime_error(std::string("packMechanism: ") + what + " does not start at 0");
+        for (int i = 0; i < rows; i++) {
+            if (ptr[i + 1] < ptr[i]) throw std::runtime_error(std::string("packMechanism: ") + what + " is not monotone");
+        }
+        if (idx) {
+            for (int j = 0; j < ptr[rows]; j++) {
+                if (idx[j] < 0 || idx[j] >= bound) {
+                    throw std::runtime_error(std::string("packMechanism: ") + what + " has a species index out of range");
+                }
+            }
+        }
+    };
+    checkCsr("reac_ptr/reac_species", t.reac_ptr, t.reac_species, R, K);
+    checkCsr("prod_ptr/prod_species", t.prod_ptr, t.prod_species, R, K);
+    checkCsr("tb_ptr/tb_species", t.tb_ptr, t.tb_species, R, K);
+    checkCsr("plog_ptr", t.plog_ptr, nullptr, R, 0);
+    checkCsr("cheb_ptr", t.cheb_ptr, nullptr, R, 0);
+    for (int i = 0; i < R; i++) {
+        if (t.rxn_type[i] == CTB_RATE_CHEBYSHEV && (long long) t.cheb_nT[i] * t.cheb_nP[i] != t.cheb_ptr[i + 1] - t.cheb_ptr[i]) {
+            throw std::runtime_error("packMechanism: Chebyshev coefficient count does not match nT x nP");
+        }
+    }
     PackedMech pm;
     MechView& v = pm.v;
     std::memset(&v, 0, sizeof(v));
@@ -335,6 +360,10 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         for (int e = 0; e < R; e++) {
             tv.maxAbsB = std::max(tv.maxAbsB, std::abs(b[e]));
             tv.maxAbsEaR = std::max(tv.maxAbsEaR, std::abs(EaR[e]));
+        }
+        for (size_t a = 0; a + 2 < fallLow.size(); a += 3) { // low-pressure limits of the falloff reactions
+            tv.maxAbsB = std::max(tv.maxAbsB, std::abs(fallLow[a + 1]));
+            tv.maxAbsEaR = std::max(tv.maxAbsEaR, std::abs(fallLow[a + 2]));
         }
         Blob tb;
         std::vector<Sp2> sp(K);
