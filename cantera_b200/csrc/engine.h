@@ -32,6 +32,15 @@ struct DevBuf {
     template <class T> T* as() { return static_cast<T*>(p); }
 };
 
+//! Pinned host memory (cudaHostAlloc): the staging ring of host-memory calls with pageable buffers.
+struct PinBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    void reserve(size_t n);
+    ~PinBuf();
+    template <class T> T* as() { return static_cast<T*>(p); }
+};
+
 struct RateOutputs {
     double* wdot = nullptr;
     double* cdot = nullptr;
@@ -81,6 +90,8 @@ public:
 
 private:
     void uploadMultipliers();
+    void ratesPageable(long long N, const double* T, const double* P, const double* Y, long long ldY,
+                       const RateOutputs& out, bool full);
     cantera_b200::MechTables m_tables;
     PackedMech m_packed;
     DeviceMech m_dev;
@@ -93,6 +104,7 @@ private:
     bool m_skip3b = false, m_skipFalloff = false;
     double m_rtolDelta = 1e-8;
     DevBuf m_stage[NSTAGE]; // device staging for host-memory calls
+    PinBuf m_pin[NSTAGE];   // pinned ring for pageable host buffers (rates)
     DevBuf m_jacScratch[NSTAGE + 1]; // per-stream scratch of the Jacobian tile kernel (last: the handle's own stream)
 };
 

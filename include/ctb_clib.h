@@ -16,8 +16,11 @@
  *
  * Batch layout: T[n], P[n] and Y[n*ldY + k] (one state per row, species contiguous; ldY >= K).
  * Per-state outputs use the same row layout with their own leading dimension.
- * memspace: CTB_HOST (0) = host pointers (pageable or pinned; the library copies in chunks through
- *           device staging buffers, see DESIGN.md "End-to-end path");
+ * memspace: CTB_HOST (0) = host pointers; the library copies in chunks through device staging buffers on
+ *           four streams (DESIGN.md "End-to-end path"). Pinned buffers (cudaHostAlloc / cudaHostRegister)
+ *           are read and written by the DMA engines directly; pageable buffers of the rate getters go
+ *           through the handle's own pinned ring (packed and unpacked by host threads, about a third of
+ *           the pinned throughput); pageable buffers of the other calls are staged by the driver;
  *           CTB_DEVICE (1) = device pointers on the handle's device, no copies.
  *
  * There is no CPU fallback: if no CUDA device is usable every constructor fails with -1.
