@@ -239,6 +239,23 @@ class BatchedGasKinetics:
     def net_production_rates_ddCi(self, T, P, Y, out=None):
         return self._jac(self._lib.ctb_kin_getNetProductionRates_ddCi, T, P, Y, out)
 
+    def net_production_rates_ddX_no_alloc(self, T, P, Y, out):
+        """net_production_rates_ddX for callers that may not allocate device memory
+        (ctb_kin_getNetProductionRates_ddX_noAlloc: static scratch array, at most clib.NOALLOC_MAX_STATES
+        states per call, calls must not overlap on the GPU). CUDA float64 tensors only, contiguous, and
+        ``out`` [N, K, K] is the caller's: nothing is allocated here either."""
+        if not (_is_torch(T) and _is_torch(P) and _is_torch(Y) and _is_torch(out)):
+            raise clib.CtbError("net_production_rates_ddX_no_alloc takes CUDA tensors (device memory only)")
+        import torch
+        K = self.n_species
+        for x in (T, P, Y, out):
+            if not (x.is_cuda and x.dtype == torch.float64 and x.is_contiguous()):
+                raise clib.CtbError("net_production_rates_ddX_no_alloc: contiguous CUDA float64 tensors only")
+        clib.check(self._lib.ctb_kin_setStream(self._h, torch.cuda.current_stream().cuda_stream))
+        clib.check(self._lib.ctb_kin_getNetProductionRates_ddX_noAlloc(
+            self._h, T.numel(), T.data_ptr(), P.data_ptr(), Y.data_ptr(), Y.shape[-1], out.data_ptr(), out.numel()))
+        return out
+
 
 REACTOR_TYPES = ("IdealGasConstPressureMoleReactor", "IdealGasMoleReactor", "IdealGasReactor",
                  "IdealGasConstPressureReactor")

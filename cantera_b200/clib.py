@@ -16,6 +16,8 @@ ERR = -999
 DERR = -999.999
 HOST, DEVICE = 0, 1
 NSTATS = 8
+NOALLOC_MAX_STATES = 1 << 22      # CTB_NOALLOC_MAX_STATES
+NOALLOC_SCRATCH_BYTES = 32 << 20  # CTB_NOALLOC_SCRATCH_BYTES
 
 _dp = C.c_void_p  # host or device pointer, by memspace
 _i32, _i64, _f64 = C.c_int32, C.c_int64, C.c_double
@@ -51,6 +53,7 @@ SIGNATURES = {
     "ctb_kin_getQuantity": (_i32, [_i32, _i32, _i64, _dp, _dp, _dp, _i64, _dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddX": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddCi": (_i32, _STATE + [_dp, _i64, _i32]),
+    "ctb_kin_getNetProductionRates_ddX_noAlloc": (_i32, _STATE + [_dp, _i64]),
     "ctb_reactornet_new": (_i32, [_i32, _i64]),
     "ctb_reactornet_newTyped": (_i32, [_i32, _i64, _i32]),
     "ctb_reactornet_nEquations": (_i32, [_i32]),

@@ -345,6 +345,16 @@ int32_t ctb_kin_getNetProductionRates_ddCi(int32_t handle, int64_t nStates, cons
     });
 }
 
+int32_t ctb_kin_getNetProductionRates_ddX_noAlloc(int32_t handle, int64_t nStates, const double* T,
+                                                  const double* P, const double* Y, int64_t ldY, double* jac,
+                                                  int64_t bufLen)
+{
+    return guard([&] {
+        KinCabinet::at(handle)->jacobianNoAlloc(nStates, T, P, Y, ldY, jac, bufLen);
+        return 0;
+    });
+}
+
 // ---- BatchReactorNet -----------------------------------------------------------------------
 
 int32_t ctb_reactornet_new(int32_t kinHandle, int64_t nReactors)

@@ -471,4 +471,33 @@ void BatchedGasKinetics::jacobian(long long N, const double* T, const double* P,
     for (int i = 0; i < NSTAGE; i++) cudaCheck(cudaStreamSynchronize(m_copyStream[i]), "cudaStreamSynchronize");
 }
 
+void BatchedGasKinetics::jacobianNoAlloc(long long N, const double* T, const double* P, const double* Y, long long ldY,
+                                         double* jac, long long bufLen)
+{
+    const char* where = "BatchedGasKinetics::jacobianNoAlloc";
+    const int K = nSpecies();
+    if (N < 0) throw CtbError(where, "negative number of states");
+    if (N > (long long) CTB_NOALLOC_MAX_STATES) {
+        throw CtbError(where, std::to_string(N) + " states exceed the maximum of " + std::to_string(CTB_NOALLOC_MAX_STATES)
+                       + " per call (CTB_NOALLOC_MAX_STATES); split the batch or use ctb_kin_getNetProductionRates_ddX");
+    }
+    if (N == 0) return;
+    if (!T || !P || !Y || !jac) throw CtbError(where, "null pointer");
+    if (ldY < K) throw CtbError(where, "ldY is smaller than the number of species");
+    if (bufLen < N * (long long) K * K) {
+        throw CtbError(where, "array size (" + std::to_string(bufLen) + ") is too small; needs "
+                       + std::to_string(N * (long long) K * K));
+    }
+    cudaCheck(cudaSetDevice(m_dev.device), "cudaSetDevice");
+    JacArgs a = {};
+    a.ddCi = 0; a.skipThirdBodies = m_skip3b; a.skipFalloff = m_skipFalloff;
+    a.N = N; a.T = T; a.P = P; a.Y = Y; a.ldY = ldY; a.jac = jac;
+    try {
+        launchJacStatic(m_dev, a, stream());
+    } catch (std::exception& ex) {
+        throw CtbError(where, ex.what());
+    }
+    cudaCheck(cudaGetLastError(), "jacTileKernel launch (static scratch)");
+}
+
 } // namespace ctb

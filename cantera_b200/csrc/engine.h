@@ -79,6 +79,11 @@ public:
     void jacobian(long long N, const double* T, const double* P, const double* Y, long long ldY,
                   double* jac, long long bufLen, bool ddCi, int memspace);
 
+    //! netProductionRates_ddX for device pointers without any device allocation (static scratch array of
+    //! kin_kernels.cu; ctb_kin_getNetProductionRates_ddX_noAlloc).
+    void jacobianNoAlloc(long long N, const double* T, const double* P, const double* Y, long long ldY,
+                         double* jac, long long bufLen);
+
     //! One of the remaining getters (CTB_Q_* of include/ctb_clib.h: the _ddT/_ddP/_ddC families and the
     //! reaction deltas) for N states: out[n*ld + i], width K (species quantities) or R (reaction quantities).
     void quantity(int what, long long N, const double* T, const double* P, const double* Y, long long ldY,

@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <type_traits>
 #include <stdexcept>
 #include <string>
@@ -580,6 +581,72 @@ void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream, void*
         ok = launchJacT<256, true>(m, a, stream);
     }
     if (!ok) throw std::runtime_error("mechanism too large for the shared-memory Jacobian kernel");
+}
+
+// ---------------------------------------------------------------- jacobian, allocation-free launch
+
+// Scratch of launchJacStatic: one file-scope array per GPU that loads the library, held until exit
+// (include/ctb_clib.h, ctb_kin_getNetProductionRates_ddX_noAlloc). In host code the NAME below is only a
+// stand-in for the symbol; the device address comes from cudaGetSymbolAddress (jacStaticScratch()).
+static __device__ __align__(256) unsigned char g_jacStaticScratch[CTB_NOALLOC_SCRATCH_BYTES];
+
+size_t jacStaticScratchBytes()
+{
+    return sizeof(g_jacStaticScratch);
+}
+
+//! Device address of g_jacStaticScratch on `device`, which must be the current device; resolved once
+//! per device.
+static double* jacStaticScratch(int device)
+{
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static void* addr[MAXDEV] = {};
+    if (device < 0 || device >= MAXDEV) throw std::runtime_error("device index beyond the static-scratch table");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess || cur != device) {
+            throw std::runtime_error("static scratch set-up: device " + std::to_string(device) + " is not current");
+        }
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_jacStaticScratch);
+        if (e != cudaSuccess || !p) {
+            throw std::runtime_error(std::string("cudaGetSymbolAddress(static Jacobian scratch): ") + cudaGetErrorString(e));
+        }
+        addr[device] = p;
+    }
+    return static_cast<double*>(addr[device]);
+}
+
+void launchJacStatic(const DeviceMech& m, const JacArgs& a, cudaStream_t stream)
+{
+    if (a.N <= 0) return;
+    const TileView& tv = m.tile;
+    const JacTilePlan full = planJacTile(m, a.N);
+    if (full.tiles == 0) throw std::runtime_error("the mechanism does not fit the Jacobian tile kernel");
+    const size_t perSlot = jacScratchDoubles(tv.R, tv.nTb) * 8; // one tile of 16 states in flight
+    const size_t slots = sizeof(g_jacStaticScratch) / perSlot;
+    if (slots == 0) {
+        throw std::runtime_error("the mechanism needs " + std::to_string(perSlot) + " bytes of scratch per tile; the static "
+                                 "array holds " + std::to_string(sizeof(g_jacStaticScratch)));
+    }
+    // as many tiles in flight as the array holds: the kernel strides over the tiles, so a smaller grid
+    // only lowers the parallelism
+    const long long nTiles = (a.N + CTB_TS - 1) / CTB_TS;
+    int tiles = 1, grid = 1;
+    long long best = 0;
+    for (int t = 1; t <= full.tiles; t++) {
+        const long long g = std::min<long long>(std::min<long long>((nTiles + t - 1) / t, m.numSMs), (long long) (slots / t));
+        if (g >= 1 && g * t > best) { best = g * t; tiles = t; grid = (int) g; }
+    }
+    const size_t smemBytes = full.tableBytes + 128 + (size_t) tiles * full.tileDoubles * 8;
+    double* scratch = jacStaticScratch(m.device);
+    auto kern = jacTileKernel<JAC_TILE_W, JAC_TILE_MAXT>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smemBytes);
+    kern<<<grid, tiles * JAC_TILE_W * 32, smemBytes, stream>>>(m.tile, m.dBlob, a, scratch, (int) full.tileDoubles,
+                                                               (int) full.tableBytes);
 }
 
 } // namespace ctb

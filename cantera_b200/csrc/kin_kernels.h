@@ -61,5 +61,9 @@ size_t jacScratchBytes(const DeviceMech& m);
 //! scratch: jacScratchBytes() of device memory owned by this launch until it completes (nullptr:
 //! the lane-group kernel of rates.cuh is used).
 void launchJac(const DeviceMech& m, const JacArgs& a, cudaStream_t stream, void* scratch);
+//! The Jacobian tile kernel on the library's static scratch array (CTB_NOALLOC_SCRATCH_BYTES per GPU): no
+//! allocation; m.device must be current. Throws when the mechanism does not fit.
+void launchJacStatic(const DeviceMech& m, const JacArgs& a, cudaStream_t stream);
+size_t jacStaticScratchBytes();
 
 } // namespace ctb

@@ -197,6 +197,27 @@ int32_t ctb_kin_getNetProductionRates_ddCi(int32_t handle, int64_t nStates, cons
                                            const double* P, const double* Y, int64_t ldY,
                                            double* jac, int64_t bufLen, int32_t memspace);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that may not
+ * allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). Same result as ctb_kin_getNetProductionRates_ddX with memspace = CTB_DEVICE (device
+ * pointers only; queued on the handle's stream; derivative settings honoured), but the call makes NO
+ * cudaMalloc / cudaFree / allocating library call: the Jacobian tile kernel's global scratch is a
+ * file-scope static __device__ array of CTB_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds
+ * until exit, and the grid is sized to the tiles that array holds (fewer tiles in flight than the
+ * allocating entry point for large mechanisms: same numbers, lower throughput).
+ * Limits, rejected with -1 and a message: nStates > CTB_NOALLOC_MAX_STATES; a mechanism whose scratch for
+ * ONE tile of 16 states, (3 R + 1 + nThirdBody) * 128 bytes, exceeds the array; a mechanism that does not
+ * fit the tile kernel's shared memory.
+ * Every call on a device shares the one array (also across handles): calls that overlap on the GPU
+ * (different streams, no dependency) RACE; serialise them. Nothing has to be cleared between calls: each
+ * launch rewrites all it reads, including the one row that must be zero. The first call on a device
+ * resolves the array's address (cudaGetSymbolAddress) and loads the kernel: make it before a capture. */
+#define CTB_NOALLOC_SCRATCH_BYTES (32 * 1024 * 1024)
+#define CTB_NOALLOC_MAX_STATES (1 << 22)
+int32_t ctb_kin_getNetProductionRates_ddX_noAlloc(int32_t handle, int64_t nStates, const double* T,
+                                                  const double* P, const double* Y, int64_t ldY,
+                                                  double* jac, int64_t bufLen);
+
 /* The remaining Kinetics getters, one entry point: out[n*ld + i] with row width R (reaction quantities)
  * or K (species quantities). quantity = CTB_Q_*:
  *   getFwdRateConstants_ddT/_ddP/_ddC, get{Fwd,Rev,Net}RatesOfProgress_ddT/_ddP/_ddC (BulkKinetics.cpp:284-385),
