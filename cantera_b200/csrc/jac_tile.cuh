@@ -89,6 +89,22 @@ __device__ __forceinline__ double sideDerivTile(const TileView& tv, const Tile& 
 __device__ __forceinline__ void scatterTile(const TileView& tv, const Tile& t, const Rx2Regs& r, double* colS, double val)
 {
     unsigned char* cb = reinterpret_cast<unsigned char*>(colS);
+    if (r.hints & RX2_HINT_DISTINCT) {
+        // all slots name different rows: six independent read-modify-writes, loads first (the same
+        // arithmetic as the chain below, without its serial shared-memory latency)
+        double* q[6] = {reinterpret_cast<double*>(cb + r.ir[0]), reinterpret_cast<double*>(cb + r.ir[1]),
+                        reinterpret_cast<double*>(cb + r.ir[2]), reinterpret_cast<double*>(cb + r.ip[0]),
+                        reinterpret_cast<double*>(cb + r.ip[1]), reinterpret_cast<double*>(cb + r.ip[2])};
+        const bool on[6] = {r.nr >= 1, r.nr >= 2, r.nr >= 3, r.np >= 1, r.np >= 2, r.np >= 3};
+        double v[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) v[i] = on[i] ? *q[i] : 0.0;
+#pragma unroll
+        for (int i = 0; i < 3; i++) if (on[i]) *q[i] = v[i] - val;
+#pragma unroll
+        for (int i = 3; i < 6; i++) if (on[i]) *q[i] = v[i] + val;
+        return;
+    }
     if (r.nr == SIDE_GENERAL) {
         const int32_t* ptr = CTB_TAB(int32_t, t.tp, tv.o_genPtr);
         const uint16_t* sp = CTB_TAB(uint16_t, t.tp, tv.o_genSp);
@@ -190,7 +206,8 @@ __device__ __forceinline__ void ropJacTile(const TileView& tv, const Tile& t, co
                     const double* st = CTB_TAB(double, tp, tv.o_genStoich);
                     for (int i = ptr[r.ip[0]]; i < ptr[r.ip[0] + 1]; i++) dg += st[i] * log(t.vS[sp[i] * CTB_LDC]);
                 } else {
-                    for (int i = 0; i < r.np; i++) dg += log(ldOff(t.vS, r.ip[i]));
+#pragma unroll
+                    for (int i = 0; i < 3; i++) if (i < r.np) dg += log(ldOff(t.vS, r.ip[i])); // constant indices: registers
                 }
             }
             rk = fmin(expSafe(dg), CTB_BIG);
@@ -274,31 +291,53 @@ __device__ __forceinline__ void jacColumnsTile(const TileView& tv, const Tile& t
     const int32_t* tptr = CTB_TAB(int32_t, t.tp, tv.o_tbTPtr);
     const uint16_t* trxn = CTB_TAB(uint16_t, t.tp, tv.o_tbTRxn);
     const double* teff = CTB_TAB(double, t.tp, tv.o_tbTEff);
+    const uint16_t* tw = CTB_TAB(uint16_t, t.tp, tv.o_tbTW);
     const unsigned char* rx = t.tp + tv.o_rx;
     for (int ci = lanePtr[j]; ci < lanePtr[j + 1]; ci++) {
         const int jc = order[ci];
         const uint32_t joff = (uint32_t) jc * CTB_LDC * 8u;
         for (int k = 0; k < tv.K; k++) colS[k * CTB_LDC] = 0.0;
-        for (int i = cptr[jc]; i < cptr[jc + 1]; i++) {
-            const GatherEnt ge = cent[i];
-            const int e = ge.rxn;
-            Rx2Regs r;
-            loadRx<true, true>(rx, e, r);
-            double d;
-            if (ge.nu > 0) { // product side: -d ropr / d c_j (reversible reactions only)
-                if (!(r.flags & CTB_RXN_REVERSIBLE)) continue;
-                d = -sideDerivTile(tv, t, r.np, r.ip, jr.krM[e * CTB_TS], jc, joff);
-            } else {
-                d = sideDerivTile(tv, t, r.nr, r.ir, jr.kfM[e * CTB_TS], jc, joff);
+        // The coefficient rows live in the L2 scratch: an item's coefficient is requested two items ahead,
+        // so that its latency is covered by the work on the items before it (the list holds no item of
+        // an irreversible reaction's product side: mech_pack.cpp).
+        const int iEnd = cptr[jc + 1];
+        int i = cptr[jc];
+        GatherEnt g1 = {0, 0}, g2 = {0, 0};
+        double k1 = 0.0, k2 = 0.0;
+        if (i < iEnd) {
+            g1 = cent[i];
+            k1 = (g1.nu > 0 ? jr.krM : jr.kfM)[g1.rxn * CTB_TS];
+        }
+        if (i + 1 < iEnd) {
+            g2 = cent[i + 1];
+            k2 = (g2.nu > 0 ? jr.krM : jr.kfM)[g2.rxn * CTB_TS];
+        }
+        for (; i < iEnd; i++) {
+            const GatherEnt ge = g1;
+            const double kM = k1;
+            g1 = g2;
+            k1 = k2;
+            if (i + 2 < iEnd) {
+                g2 = cent[i + 2];
+                k2 = (g2.nu > 0 ? jr.krM : jr.kfM)[g2.rxn * CTB_TS];
             }
+            Rx2Regs r;
+            loadRx<true, true>(rx, ge.rxn, r);
+            // product side: -d ropr / d c_j; reactant side: d ropf / d c_j
+            const double d = ge.nu > 0 ? -sideDerivTile(tv, t, r.np, r.ip, kM, jc, joff)
+                                       : sideDerivTile(tv, t, r.nr, r.ir, kM, jc, joff);
             scatterTile(tv, t, r, colS, d);
         }
         if (!skip3b) { // explicit efficiencies: ThirdBodyCalc::derivatives (ThirdBodyCalc.h:97-100)
-            for (int i = tptr[jc]; i < tptr[jc + 1]; i++) {
-                const int e = trxn[i];
+            const int tEnd = tptr[jc + 1];
+            int it = tptr[jc];
+            double w1 = it < tEnd ? jr.we[tw[it] * CTB_TS] : 0.0; // one entry ahead, as above
+            for (; it < tEnd; it++) {
+                const double we = w1;
+                if (it + 1 < tEnd) w1 = jr.we[tw[it + 1] * CTB_TS];
                 Rx2Regs r;
-                loadRx<true, true>(rx, e, r);
-                scatterTile(tv, t, r, colS, jr.we[r.tbIdx * CTB_TS] * teff[i]);
+                loadRx<true, true>(rx, trxn[it], r);
+                scatterTile(tv, t, r, colS, we * teff[it]);
             }
         }
         out(jc);

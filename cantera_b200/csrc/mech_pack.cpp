@@ -397,6 +397,12 @@ PackedMech packMechanism(const ctb_mech_tables& t)
             x.p0 = slot(rec[e].np, spd, 0); x.p1 = slot(rec[e].np, spd, 1); x.p2 = slot(rec[e].np, spd, 2);
             x.nr = rec[e].nr; x.np = rec[e].np; x.cls = rec[e].cls; x.flags = rec[e].flags;
             x.tbIdx = tbIdx[e]; x.auxIdx = auxIdx[e];
+            if (rec[e].nr != SIDE_GENERAL && rec[e].np != SIDE_GENERAL) {
+                std::vector<uint16_t> all(sr, sr + rec[e].nr);
+                all.insert(all.end(), spd, spd + rec[e].np);
+                std::sort(all.begin(), all.end());
+                if (std::adjacent_find(all.begin(), all.end()) == all.end()) x.hints |= RX2_HINT_DISTINCT;
+            }
         }
         {
             // aux ordinals are per class family (falloff / plog / chebyshev count separately): one
@@ -484,13 +490,29 @@ PackedMech packMechanism(const ctb_mech_tables& t)
         tv.bytes = (uint32_t) tb.data.size();
         // Jacobian-only tables
         putDeal(0);
-        tv.o_colPtr = tb.put(gPtr); tv.o_colEnt = tb.put(gEnt);
+        // column items of the Jacobian: the gather entries without the product side of irreversible
+        // reactions (their reverse rate of progress is identically zero)
+        std::vector<int32_t> cPtr{0};
+        std::vector<GatherEnt> cEnt;
+        for (int k = 0; k < K; k++) {
+            for (int i = gPtr[k]; i < gPtr[k + 1]; i++) {
+                if (gEnt[i].nu > 0 && !(rec[gEnt[i].rxn].flags & CTB_RXN_REVERSIBLE)) continue;
+                cEnt.push_back(gEnt[i]);
+            }
+            cPtr.push_back((int32_t) cEnt.size());
+        }
+        tv.o_colPtr = tb.put(cPtr); tv.o_colEnt = tb.put(cEnt);
         tv.o_tbTPtr = tb.put(tbTPtr); tv.o_tbTRxn = tb.put(tbTRxn); tv.o_tbTEff = tb.put(tbTEff);
+        {
+            std::vector<uint16_t> tbTW;
+            for (uint16_t e : tbTRxn) tbTW.push_back((uint16_t) tbIdx[e]);
+            tv.o_tbTW = tb.put(tbTW);
+        }
         for (int d = 0; d < 2; d++) {
             const int NL = 4 << d;
             std::vector<int> order(K);
             std::iota(order.begin(), order.end(), 0);
-            auto cost = [&](int k) { return (long long) (gPtr[k + 1] - gPtr[k]) + (tbTPtr[k + 1] - tbTPtr[k]) + 4; };
+            auto cost = [&](int k) { return (long long) (cPtr[k + 1] - cPtr[k]) + (tbTPtr[k + 1] - tbTPtr[k]) + 4; };
             std::stable_sort(order.begin(), order.end(), [&](int a, int b2) { return cost(a) > cost(b2); });
             std::vector<std::vector<int>> lane(NL);
             std::vector<long long> load(NL, 0);

@@ -169,8 +169,11 @@ struct Rx2 {
     uint8_t nr, np, cls, flags; // word 3
     int16_t tbIdx, auxIdx;
     uint32_t auxMultIdx;      // ordinal into the auxMult table (non-Arrhenius classes)
-    uint32_t pad;
+    uint32_t hints;           // RX2_HINT_*
 };
+//! every side has at most three unit slots and all slots of the reaction name different species: the
+//! read-modify-writes of its stoichiometric column are independent (jac_tile.cuh scatterTile)
+#define RX2_HINT_DISTINCT 1u
 static_assert(sizeof(Rx2) == 64, "Rx2 must be 64 bytes");
 
 // gather record of one species, 16 bytes: its entries are QUADS of 32-bit byte offsets of q rows
@@ -224,6 +227,7 @@ struct TileView {
     uint32_t o_colEnt;   // GatherEnt[]
     uint32_t o_tbTPtr;   // int32[K+1]: explicit third-body efficiencies transposed (species-major)
     uint32_t o_tbTRxn;   // uint16[]
+    uint32_t o_tbTW;     // uint16[] third-body ordinal (row of the we scratch) of the same entries
     uint32_t o_tbTEff;   // double[] (eff - default)
     uint32_t o_colLane[2];  // int32[NL+1] for NL = 4, 8: columns dealt to the lanes, balanced by item count
     uint32_t o_colOrder[2]; // uint16[K]
