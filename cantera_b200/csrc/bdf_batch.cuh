@@ -128,6 +128,67 @@ struct Solo {
     CTB_HD double max(double x) const { return x; }
 };
 
+#ifdef __CUDACC__
+// ---- warp-level TMA helpers (1-D bulk copies completing on an mbarrier)
+__device__ __forceinline__ void bulkLoad(void* dstSmem, const void* srcGlobal, uint32_t bytes, unsigned long long* bar)
+{
+    const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
+    const uint32_t dstAddr = (uint32_t) __cvta_generic_to_shared(dstSmem);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barAddr), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dstAddr), "l"(srcGlobal), "r"(bytes), "r"(barAddr)
+                 : "memory");
+}
+__device__ __forceinline__ void barWait(unsigned long long* bar, uint32_t parity)
+{
+    const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(barAddr), "r"(parity)
+            : "memory");
+    }
+}
+#endif
+
+//! Per-warp shared-memory ring through which the control kernel streams the slot's Newton-matrix inverse
+//! for the matrix-vector product of the Newton solve: NBUF chunks of chunkCols columns in flight as TMA
+//! bulk copies (no registers held across the DRAM latency), the first NBUF requested together with the
+//! slot's prefix at the start of the visit.
+struct MatRing {
+    static constexpr int NBUF = 3;
+    double* buf;              // NBUF x chunkCols x n doubles of shared memory
+    unsigned long long* bar;  // NBUF mbarriers
+    const unsigned char* src; // the slot's matrix in HBM
+    int chunkCols, nChunks;
+    uint32_t chunkBytes, lastBytes; // multiples of 16
+    uint32_t parity;          // bit i: phase parity of barrier i (persists across the warp's visits)
+#ifdef __CUDACC__
+    __device__ __forceinline__ void request(int ch) const {
+        const int bi = ch % NBUF;
+        bulkLoad(reinterpret_cast<unsigned char*>(buf) + (size_t) bi * chunkBytes, src + (size_t) ch * chunkBytes,
+                 ch == nChunks - 1 ? lastBytes : chunkBytes, bar + bi);
+    }
+    //! lane 0, at the start of a visit that resumes in the Newton solve
+    __device__ __forceinline__ void prime(const unsigned char* matrix) {
+        src = matrix;
+        for (int ch = 0; ch < NBUF && ch < nChunks; ch++) request(ch);
+    }
+    __device__ __forceinline__ void wait(int bi) {
+        barWait(bar + bi, (parity >> bi) & 1u);
+        parity ^= 1u << bi;
+    }
+    //! consumes the primed chunks without using them (the visit leaves the Newton solve early)
+    __device__ __forceinline__ void drain() {
+        for (int ch = 0; ch < NBUF && ch < nChunks; ch++) wait(ch);
+    }
+#endif
+};
+
 //! One cooperative group G (a warp on the device) advances slot s until it needs a right-hand
 //! side (returns with ctl.pc set) or runs out of reactors. Controller scalars are replicated in
 //! every lane (reductions return identical values), vectors are distributed lane-cyclically:
@@ -142,6 +203,7 @@ struct BatchBdf {
     double* const vec;       // the slot's vectors, likewise
     const double* const MPtr; // (I - gamma J)^-1 of the slot, column-major, in HBM
     double* const xs;  // n doubles of scratch (only used by the one-lane solve)
+    MatRing* const ring; // shared-memory ring of the matrix-vector product, or null: loads through registers
 #ifdef CTB_CTL_IN_SMEM
     BatchCtl& c;       // controller memory is used where it lies (shared memory): fewer registers
 #else
@@ -150,9 +212,9 @@ struct BatchBdf {
 
     //! blk: the slot's [ctl | vec] prefix wherever it currently lives; Minv: the slot's matrix
     CTB_HD BatchBdf(const G& g_, const ReactorBatch& p_, const SlotMem& m_, int s_, unsigned char* blk,
-                    const double* Minv, double* xs_)
+                    const double* Minv, double* xs_, MatRing* ring_ = nullptr)
         : g(g_), p(p_), mem(m_), n(p_.neq), s(s_), ctlPtr(reinterpret_cast<BatchCtl*>(blk)),
-          vec(reinterpret_cast<double*>(blk + m_.oVec)), MPtr(Minv), xs(xs_)
+          vec(reinterpret_cast<double*>(blk + m_.oVec)), MPtr(Minv), xs(xs_), ring(ring_)
 #ifdef CTB_CTL_IN_SMEM
           , c(*reinterpret_cast<BatchCtl*>(blk))
 #endif
@@ -486,6 +548,47 @@ struct BatchBdf {
 #pragma unroll
         for (int j = 0; j < NPL; j++) xr[j] = a0[j] + a1[j];
     }
+
+    //! The same product with the matrix arriving through the shared-memory ring (MatRing): chunk ch + NBUF is
+    //! requested as soon as chunk ch has been consumed. chunkCols is even: even columns feed a0, odd ones a1.
+    __device__ __forceinline__ void gemvRing(double (&xr)[NPL]) const {
+        const int lane = g.lane();
+        const double* __restrict__ b = vec + 9 * n;
+        const bool lastOk = lane + 32 * (NPL - 1) < n;
+        double a0[NPL], a1[NPL];
+#pragma unroll
+        for (int j = 0; j < NPL; j++) { a0[j] = 0.0; a1[j] = 0.0; }
+        MatRing& rg = *ring;
+        const int cc = rg.chunkCols;
+        int bi = 0;
+#pragma unroll 1
+        for (int ch = 0, c0 = 0; ch < rg.nChunks; ch++, c0 += cc) {
+            rg.wait(bi);
+            const double* __restrict__ mc = rg.buf + (size_t) bi * (rg.chunkBytes >> 3) + lane;
+            const int nc = min(cc, n - c0);
+            int u = 0;
+#pragma unroll 2
+            for (; u + 2 <= nc; u += 2) {
+                const double b0 = b[c0 + u], b1 = b[c0 + u + 1];
+#pragma unroll
+                for (int j = 0; j < NPL; j++) {
+                    const bool ok = j < NPL - 1 || lastOk;
+                    a0[j] = fma(ok ? mc[(size_t) u * n + 32 * j] : 0.0, b0, a0[j]);
+                    a1[j] = fma(ok ? mc[(size_t) (u + 1) * n + 32 * j] : 0.0, b1, a1[j]);
+                }
+            }
+            if (u < nc) {
+                const double b0 = b[c0 + u];
+#pragma unroll
+                for (int j = 0; j < NPL; j++) a0[j] = fma((j < NPL - 1 || lastOk) ? mc[(size_t) u * n + 32 * j] : 0.0, b0, a0[j]);
+            }
+            __syncwarp(); // every lane has read the buffer before it is refilled
+            if (lane == 0 && ch + MatRing::NBUF < rg.nChunks) rg.request(ch + MatRing::NBUF);
+            bi = bi + 1 == MatRing::NBUF ? 0 : bi + 1;
+        }
+#pragma unroll
+        for (int j = 0; j < NPL; j++) xr[j] = a0[j] + a1[j];
+    }
 #endif
 
     CTB_HD void finish(int status) {
@@ -754,6 +857,9 @@ struct BatchBdf {
                 if (c.needSing) {
                     c.needSing = 0;
                     if (c.sing) {
+#ifdef __CUDA_ARCH__
+                        if (ring) ring->drain();
+#endif
                         st = X_NLS_FAIL;
                         continue;
                     }
@@ -768,7 +874,7 @@ struct BatchBdf {
                     CTB_FOR_OWN(i) F(i) = c.gamma * F(i) - (c.rl1 * ZN(1, i) + AC(i));
                     g.sync();
                     double xr[NPL];
-                    gemvWarp(xr);
+                    if (ring) gemvRing(xr); else gemvWarp(xr);
 #pragma unroll
                     for (int j = 0; j < NPL; j++) {
                         const int i = g.lane() + G::NT * j;

@@ -63,30 +63,7 @@ __global__ void batchAbortKernel(ReactorBatch b, SlotMem mem)
     if (r < b.N) b.status[r] = CTB_STATUS_TOO_MANY_STEPS;
 }
 
-// ---- warp-level TMA helpers (1-D bulk copies, one mbarrier per warp)
-__device__ __forceinline__ void bulkLoad(void* dstSmem, const void* srcGlobal, uint32_t bytes, unsigned long long* bar)
-{
-    const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
-    const uint32_t dstAddr = (uint32_t) __cvta_generic_to_shared(dstSmem);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barAddr), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dstAddr), "l"(srcGlobal), "r"(bytes), "r"(barAddr)
-                 : "memory");
-}
-__device__ __forceinline__ void barWait(unsigned long long* bar, uint32_t parity)
-{
-    const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
-    uint32_t done = 0;
-    while (!done) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(barAddr), "r"(parity)
-            : "memory");
-    }
-}
+// ---- warp-level TMA helpers (bulkLoad and barWait live in bdf_batch.cuh: the Newton solve uses them too)
 __device__ __forceinline__ void bulkStore(void* dstGlobal, const void* srcSmem, uint32_t bytes)
 {
     const uint32_t srcAddr = (uint32_t) __cvta_generic_to_shared(srcSmem);
@@ -111,16 +88,29 @@ __device__ __forceinline__ void prefetchL2(const void* srcGlobal, uint32_t bytes
 //! product) and writes the prefix back with a bulk store. The other warps of the CTA cover the
 //! latencies; the matrix never occupies shared memory, so 16 warps per SM are resident.
 template <int NPL>
-__global__ void __launch_bounds__(CTB_CTL_WARPS * 32, 1) batchControlKernel(const ReactorBatch b, const SlotMem mem)
+__global__ void __launch_bounds__(CTB_CTL_WARPS * 32, 1) batchControlKernel(const ReactorBatch b, const SlotMem mem, const int ringCols)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
     const uint32_t prefix = mem.oM; // ctl + vec
     unsigned char* buf = smem + (size_t) warp * prefix;
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * prefix) + warp;
+    // [W prefixes][W x (1 + NBUF) mbarriers][W matrix rings]
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t) W * prefix) + (size_t) warp * (1 + MatRing::NBUF);
+    MatRing ring;
+    ring.chunkCols = ringCols;
+    ring.chunkBytes = (uint32_t) ringCols * (uint32_t) mem.n * 8u;
+    ring.nChunks = ringCols > 0 ? (mem.n + ringCols - 1) / ringCols : 0;
+    ring.lastBytes = ringCols > 0 ? (((uint32_t) (mem.n - (ring.nChunks - 1) * ringCols) * (uint32_t) mem.n * 8u + 15u) & ~15u) : 0u;
+    ring.bar = bar + 1;
+    ring.buf = reinterpret_cast<double*>(smem + (((size_t) W * prefix + (size_t) W * (1 + MatRing::NBUF) * 8 + 127) & ~(size_t) 127)
+                                         + (size_t) warp * MatRing::NBUF * ring.chunkBytes);
+    ring.parity = 0;
+    ring.src = nullptr;
     if (lane == 0) {
-        const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar);
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
+        for (int i = 0; i < 1 + MatRing::NBUF; i++) {
+            const uint32_t barAddr = (uint32_t) __cvta_generic_to_shared(bar + i);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) mem.setupCount[mem.parity ^ 1] = 0; // next round's list
@@ -133,15 +123,18 @@ __global__ void __launch_bounds__(CTB_CTL_WARPS * 32, 1) batchControlKernel(cons
         if (pc == PC_IDLE) continue;
         unsigned char* gblk = mem.block(s);
         const long long t0 = mem.prof ? clock64() : 0;
+        // the visit resumes in the Newton solve: its matrix-vector product needs the slot's inverse
+        const bool useRing = ringCols > 0 && pc == PC_NEWTON;
         if (lane == 0) {
             bulkLoad(buf, gblk, prefix, bar);
-            if (pc == PC_NEWTON) prefetchL2(gblk + mem.oM, matBytes);
+            if (useRing) ring.prime(gblk + mem.oM);
+            else if (pc == PC_NEWTON) prefetchL2(gblk + mem.oM, matBytes);
         }
         barWait(bar, parity);
         parity ^= 1;
         const long long t1 = mem.prof ? clock64() : 0;
         {
-            BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, buf, mem.M(s), nullptr);
+            BatchBdf<SubWarp<32>, NPL> bdf(g, b, mem, s, buf, mem.M(s), nullptr, useRing ? &ring : nullptr);
             bdf.run();
         }
         const long long t2 = mem.prof ? clock64() : 0;
@@ -751,50 +744,53 @@ __global__ void __launch_bounds__(RP, MINB) batchInvertRotKernel(const SlotMem m
         __syncthreads();
 #pragma unroll 1
         for (int k = 0; k < n; k++) {
-            double best = -1.0;
+            // Partial pivoting on the HIGH WORDS of |a[0]| (sign stripped: exponent and 20 mantissa bits order the
+            // magnitudes well enough for stability): one integer warp reduction instead of five rounds of
+            // double-precision shuffles and compares. Every warp scans the whole column and finds the same row.
+            unsigned key = 0u;
             int bi = RP;
 #pragma unroll
             for (int r = 0; r < RP / 32; r++) {
-                const double val = fabs(colbuf[lane + 32 * r]);
-                if (!((usedMask >> r) & 1u) && val > best) { best = val; bi = lane + 32 * r; }
+                const unsigned kk = ((usedMask >> r) & 1u) ? 0u : ((unsigned) __double2hiint(colbuf[lane + 32 * r]) & 0x7fffffffu);
+                if (kk > key) { key = kk; bi = lane + 32 * r; }
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-            }
-            if (!(best > 0.0) || !(best <= 1.7e308)) {
-                sing = true; // zero, NaN or infinite column: the controller retries with a smaller step
+            const unsigned kmax = __reduce_max_sync(0xffffffffu, key);
+            if (kmax == 0u || kmax >= 0x7ff00000u) {
+                sing = true; // zero (or denormal), NaN or infinite column: the controller retries with a smaller step
                 break;       // uniform: every warp sees the same column
             }
-            const int p = bi;
+            const int p = __shfl_sync(0xffffffffu, bi, __ffs(__ballot_sync(0xffffffffu, key == kmax)) - 1);
             if ((p & 31) == lane) usedMask |= 1u << (p >> 5);
-            const double f = a[0];
-            const double pinv = 1.0 / colbuf[p];
-            if (row == p) {
+            const bool isP = row == p;
+            if (isP) {
+                // the RAW pivot row (shifted by one position) goes to shared memory; the scaling by 1 / pivot is
+                // folded into every row's own multiplier, so nobody waits for this thread to scale it
                 myStep = k;
+                double2* wb = reinterpret_cast<double2*>(rowbuf);
 #pragma unroll
-                for (int j = 0; j < CPT - 1; j++) {
-                    a[j] = a[j + 1] * pinv;
-                    rowbuf[j] = a[j];
-                }
-                a[CPT - 1] = pinv;
-                rowbuf[CPT - 1] = pinv;
+                for (int j = 0; j < CPT - 2; j += 2) wb[j / 2] = make_double2(a[j + 1], a[j + 2]);
+                wb[CPT / 2 - 1] = make_double2(a[CPT - 1], 1.0);
                 piv[k] = p;
             }
+            const double pv = colbuf[p];
+            // |pivot| in [2^-1012, 2^1012]: reciprocal by the hardware seed and two Newton steps (the inverse only
+            // steers a Newton iteration), else the full division
+            const double pinv = (kmax > 0x00b00000u && kmax < 0x7f300000u) ? rcpFast(pv) : 1.0 / pv;
+            const double alpha = isP ? pinv : -(a[0] * pinv);
             __syncthreads();
-            if (row != p) {
+            {
+                // a[j] <- a[j+1] - (a[0] / pivot) raw[j]; the pivot row itself: a[j] <- raw[j] / pivot, as the
+                // same fused multiply-add on a zero addend (no divergent second loop)
                 const double2* rb = reinterpret_cast<const double2*>(rowbuf);
 #pragma unroll
                 for (int j = 0; j < CPT - 2; j += 2) {
                     const double2 r2 = rb[j / 2];
-                    a[j] = fma(-f, r2.x, a[j + 1]);
-                    a[j + 1] = fma(-f, r2.y, a[j + 2]);
+                    a[j] = fma(alpha, r2.x, isP ? 0.0 : a[j + 1]);
+                    a[j + 1] = fma(alpha, r2.y, isP ? 0.0 : a[j + 2]);
                 }
                 const double2 r2 = rb[CPT / 2 - 1];
-                a[CPT - 2] = fma(-f, r2.x, a[CPT - 1]);
-                a[CPT - 1] = -f * r2.y;
+                a[CPT - 2] = fma(alpha, r2.x, isP ? 0.0 : a[CPT - 1]);
+                a[CPT - 1] = alpha * r2.y;
             }
             colbuf[row] = a[0];
             __syncthreads();
@@ -1034,11 +1030,20 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
     // ---- control kernel: one shared-memory [ctl | vec] buffer per warp
     int ctlWarps = (int) std::min<size_t>(CTB_CTL_WARPS, (budget - 256) / mem.oM);
     if (ctlWarps < 1) throw std::runtime_error("a reactor slot does not fit in shared memory");
-    const size_t ctlSmem = (size_t) ctlWarps * mem.oM + 256;
+    // what is left of the shared memory becomes the per-warp rings of the Newton matrix (MatRing): NBUF chunks of
+    // an even number of columns; no room for two columns per chunk: the product loads through registers
+    const size_t ctlFixed = (((size_t) ctlWarps * mem.oM + (size_t) ctlWarps * (1 + MatRing::NBUF) * 8 + 127) & ~(size_t) 127);
+    int ringCols = 0;
+    if (budget > ctlFixed) {
+        const size_t perWarp = (budget - ctlFixed) / ctlWarps;
+        ringCols = (int) std::min<size_t>(perWarp / ((size_t) MatRing::NBUF * n * 8), (size_t) n) & ~1;
+    }
+    if (std::getenv("CTB_CTL_GEMV") && std::string(std::getenv("CTB_CTL_GEMV")) == "registers") ringCols = 0; // diagnostics
+    const size_t ctlSmem = ctlFixed + (size_t) ctlWarps * MatRing::NBUF * ringCols * n * 8;
     const int npl = (n + 31) / 32;
     if (npl > 4) throw std::runtime_error("more than 128 equations per reactor");
     const int ctlGrid = (int) std::max<long long>(1, std::min<long long>((S + ctlWarps - 1) / ctlWarps, m.numSMs));
-    void (*ctlKern)(const ReactorBatch, const SlotMem) =
+    void (*ctlKern)(const ReactorBatch, const SlotMem, const int) =
         npl == 1 ? batchControlKernel<1> : npl == 2 ? batchControlKernel<2> : npl == 3 ? batchControlKernel<3>
                                                                                        : batchControlKernel<4>;
     cudaFuncSetAttribute(ctlKern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctlSmem);
@@ -1058,7 +1063,7 @@ long long launchAdvanceBatch(const DeviceMech& m, const ReactorBatch& b, void* w
         cudaEvent_t* e5 = profile ? ev[rounds & 15] : nullptr;
         mem.parity = (int) (rounds & 1);
         if (e5) cudaEventRecord(e5[0], stream);
-        ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem);
+        ctlKern<<<ctlGrid, ctlWarps * 32, ctlSmem, stream>>>(b, mem, ringCols);
         if (e5) cudaEventRecord(e5[1], stream);
         if (tp.tiles > 0) {
             batchRhsTileKernel<RHS_TILE_W, RHS_TILE_MAXT, SlotIO><<<tp.grid, tp.tiles * RHS_TILE_W * 32, tp.smemBytes, stream>>>(
