@@ -116,6 +116,23 @@ class BatchedGasKinetics:
         return cls(yaml, device, _handle=clib.check(b.ctb_kin_new(-1, str(yaml).encode(), phase.encode(), device)))
 
     # ---- lifetime
+    @classmethod
+    def from_yaml_standalone(cls, yaml_path, phase="", device=0, data_dirs=()):
+        """The mechanism read from the reference's YAML format WITHOUT the reference (cantera_b200/yaml_mech.py:
+        bit-identical tables for the config mechanisms and the reference's kinetics test inputs)."""
+        import os
+        import tempfile
+        from .ctbm import write_arrays
+        from .yaml_mech import tables_from_yaml
+        tables = tables_from_yaml(yaml_path, phase, data_dirs)
+        fd, path = tempfile.mkstemp(suffix=".ctbm")
+        os.close(fd)
+        try:
+            write_arrays(path, tables)
+            return cls(path, device=device)
+        finally:
+            os.unlink(path)
+
     def close(self):
         if getattr(self, "_h", None) is not None:
             self._lib.ctb_kin_del(self._h)

@@ -160,6 +160,34 @@ def test_kin_new_in_process(yaml, phase, case, kin_cache):
     kin2.close()
 
 
+def test_kin_from_standalone_yaml_loader(kin_cache):
+    """f4: the mechanism read by cantera_b200/yaml_mech.py (no reference at run time) against the handle loaded
+    from the reference-extracted .ctbm file: the tables are identical (tests/test_yaml_mech.py), so are the
+    outputs. The toy input of tests/golden runs end to end as well."""
+    import os
+    from conftest import GOLDEN, ROOT
+    from cantera_b200 import BatchedGasKinetics
+    toy = BatchedGasKinetics.from_yaml_standalone(os.path.join(GOLDEN, "toy_mech.yaml"), "toy")
+    assert (toy.n_species, toy.n_reactions) == (5, 6)
+    w = toy.net_production_rates(np.array([1500.0]), np.array([2e5]), np.array([[0.2, 0.1, 0.3, 0.2, 0.2]]))
+    assert np.all(np.isfinite(w)) and np.any(w != 0.0)
+    toy.close()
+    path = os.path.join(ROOT, "oracle", "_ref", "data", "gri30.yaml")
+    if not os.path.exists(path):
+        pytest.skip("the reference's YAML data files are not on this machine")
+    kin2 = BatchedGasKinetics.from_yaml_standalone(path, "gri30")
+    kin = kin_cache("gri30")
+    rng = np.random.default_rng(12)
+    n, K = 513, kin.n_species
+    T = rng.uniform(800, 2500, n)
+    P = 101325.0 * rng.uniform(1, 50, n)
+    Y = rng.uniform(0, 1, (n, K))
+    Y /= Y.sum(axis=1, keepdims=True)
+    assert np.array_equal(kin2.net_production_rates(T, P, Y), kin.net_production_rates(T, P, Y))
+    assert np.array_equal(kin2.net_production_rates_ddX(T[:40], P[:40], Y[:40]), kin.net_production_rates_ddX(T[:40], P[:40], Y[:40]))
+    kin2.close()
+
+
 DERIV_CASES = ["h2o2", "gri30", "nDodecane", "pdep-test", "sri-falloff", "tsang-falloff", "chemically-activated-reaction",
                "explicit-third-bodies"]
 
