@@ -160,7 +160,7 @@ __device__ __forceinline__ void barWait(unsigned long long* bar, uint32_t parity
 //! bulk copies (no registers held across the DRAM latency), the first NBUF requested together with the
 //! slot's prefix at the start of the visit.
 struct MatRing {
-    static constexpr int NBUF = 3;
+    static constexpr int NBUF = 2;
     double* buf;              // NBUF x chunkCols x n doubles of shared memory
     unsigned long long* bar;  // NBUF mbarriers
     const unsigned char* src; // the slot's matrix in HBM
@@ -551,40 +551,51 @@ struct BatchBdf {
 
     //! The same product with the matrix arriving through the shared-memory ring (MatRing): chunk ch + NBUF is
     //! requested as soon as chunk ch has been consumed. chunkCols is even: even columns feed a0, odd ones a1.
+    //! Pointers advance by additions only (n is a run-time value), and rows past n read a clamped,
+    //! in-range element whose result is never used, so the inner loop carries no predicates.
     __device__ __forceinline__ void gemvRing(double (&xr)[NPL]) const {
         const int lane = g.lane();
-        const double* __restrict__ b = vec + 9 * n;
-        const bool lastOk = lane + 32 * (NPL - 1) < n;
+        MatRing& rg = *ring;
+        int off[NPL];
+#pragma unroll
+        for (int j = 0; j < NPL; j++) off[j] = min(lane + 32 * j, n - 1);
         double a0[NPL], a1[NPL];
 #pragma unroll
         for (int j = 0; j < NPL; j++) { a0[j] = 0.0; a1[j] = 0.0; }
-        MatRing& rg = *ring;
+        const double* __restrict__ bp = vec + 9 * n;
         const int cc = rg.chunkCols;
-        int bi = 0;
+        const uint32_t chunkDoubles = rg.chunkBytes >> 3;
+        const double* bufp = rg.buf;
+        int bi = 0, left = n;
 #pragma unroll 1
-        for (int ch = 0, c0 = 0; ch < rg.nChunks; ch++, c0 += cc) {
+        for (int ch = 0; ch < rg.nChunks; ch++) {
             rg.wait(bi);
-            const double* __restrict__ mc = rg.buf + (size_t) bi * (rg.chunkBytes >> 3) + lane;
-            const int nc = min(cc, n - c0);
+            const double* __restrict__ col = bufp;
+            const int nc = min(cc, left);
             int u = 0;
 #pragma unroll 2
             for (; u + 2 <= nc; u += 2) {
-                const double b0 = b[c0 + u], b1 = b[c0 + u + 1];
+                const double b0 = bp[0], b1 = bp[1];
+                const double* __restrict__ col1 = col + n;
 #pragma unroll
                 for (int j = 0; j < NPL; j++) {
-                    const bool ok = j < NPL - 1 || lastOk;
-                    a0[j] = fma(ok ? mc[(size_t) u * n + 32 * j] : 0.0, b0, a0[j]);
-                    a1[j] = fma(ok ? mc[(size_t) (u + 1) * n + 32 * j] : 0.0, b1, a1[j]);
+                    a0[j] = fma(col[off[j]], b0, a0[j]);
+                    a1[j] = fma(col1[off[j]], b1, a1[j]);
                 }
+                col = col1 + n;
+                bp += 2;
             }
             if (u < nc) {
-                const double b0 = b[c0 + u];
+                const double b0 = bp[0];
 #pragma unroll
-                for (int j = 0; j < NPL; j++) a0[j] = fma((j < NPL - 1 || lastOk) ? mc[(size_t) u * n + 32 * j] : 0.0, b0, a0[j]);
+                for (int j = 0; j < NPL; j++) a0[j] = fma(col[off[j]], b0, a0[j]);
+                bp += 1;
             }
+            left -= nc;
             __syncwarp(); // every lane has read the buffer before it is refilled
             if (lane == 0 && ch + MatRing::NBUF < rg.nChunks) rg.request(ch + MatRing::NBUF);
-            bi = bi + 1 == MatRing::NBUF ? 0 : bi + 1;
+            bufp += chunkDoubles;
+            if (++bi == MatRing::NBUF) { bi = 0; bufp = rg.buf; }
         }
 #pragma unroll
         for (int j = 0; j < NPL; j++) xr[j] = a0[j] + a1[j];
