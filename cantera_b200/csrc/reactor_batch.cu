@@ -962,8 +962,14 @@ long long batchSlotCap(const DeviceMech& m, int neq)
     const unsigned long long slotBytes = slotLayout(neq, tmp);
     if ((neq + 31) / 32 > 4) return 0;
     if ((unsigned long long) tmp.oM * 4 + 256 > (unsigned long long) m.smemOptIn - 1024) return 0;
-    // enough slots for several waves of every kernel, bounded by ~8 GB of slot memory
-    long long cap = (long long) m.numSMs * 512;
+    // enough slots for several waves of every kernel, bounded by ~8 GB of slot memory. 384 per SM: the 16-slot
+    // tiles of the right-hand-side kernel are then a whole number of waves (3 tiles per SM), and the slots that
+    // ask for a new Newton matrix in one round (7-8 % in an ignition batch) fit ONE pass of the Jacobian tile
+    // kernel (2 tiles per SM), whose duration is the latency of a tile whatever their number
+    // (512: 24.6 k, 448: 25.1 k, 384: 25.9 k, 320: 24.9 k gri30 reactors/s on 524 288 reactors)
+    int perSm = 384;
+    if (const char* e = std::getenv("CTB_SLOTS_PER_SM")) perSm = std::max(16, std::atoi(e)); // diagnostics: same results, other pace
+    long long cap = (long long) m.numSMs * perSm;
     cap = std::min<long long>(cap, (8LL << 30) / (long long) slotBytes);
     return std::max<long long>(cap, 1);
 }
