@@ -6,3 +6,4 @@ from .yaml_mech import MechanismError, tables_from_yaml  # noqa: F401
 
 __version__ = "0.1.0"
 from .solution_array import BatchedSolutionArray, MultiGpuKinetics, MultiGpuReactorNet  # noqa: F401,E402
+from .transport import BatchedMixTransport  # noqa: F401,E402

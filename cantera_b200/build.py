@@ -11,7 +11,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libctb.so")
 # (source, extra nvcc flags, object name); reactor_advance.cu is compiled once per group width
 SOURCES = [(s, [], s + ".o") for s in ("mech_pack.cpp", "kin_kernels.cu", "engine.cu", "reactor.cu",
-                                       "reactor_kernels.cu", "reactor_batch.cu", "ctb_clib.cu", "derivs_kernels.cu")]
+                                       "reactor_kernels.cu", "reactor_batch.cu", "ctb_clib.cu", "derivs_kernels.cu", "transport.cu")]
 SOURCES += [("reactor_advance.cu", ["-DCTB_ADV_NT=%d" % nt], "reactor_advance_%d.o" % nt) for nt in (128, 256, 64, 32)]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--fmad=true",

@@ -54,6 +54,12 @@ SIGNATURES = {
     "ctb_kin_getNetProductionRates_ddX": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddCi": (_i32, _STATE + [_dp, _i64, _i32]),
     "ctb_kin_getNetProductionRates_ddX_noAlloc": (_i32, _STATE + [_dp, _i64]),
+    "ctb_trans_newFromArrays": (_i32, [_i32, _dp, _dp, _dp, _dp, _i32]),
+    "ctb_trans_del": (_i32, [_i32]),
+    "ctb_trans_nSpecies": (_i32, [_i32]),
+    "ctb_trans_setStream": (_i32, [_i32, C.c_void_p]),
+    "ctb_trans_synchronize": (_i32, [_i32]),
+    "ctb_trans_getMixtureTransport": (_i32, _STATE + [_dp, _dp, _dp, _i64, _i32]),
     "ctb_reactornet_new": (_i32, [_i32, _i64]),
     "ctb_reactornet_newTyped": (_i32, [_i32, _i64, _i32]),
     "ctb_reactornet_nEquations": (_i32, [_i32]),

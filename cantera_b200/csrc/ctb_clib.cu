@@ -5,6 +5,7 @@
 #include "../../include/ctb_clib.h"
 #include "engine.h"
 #include "reactor.h"
+#include "transport.h"
 
 #include <cmath>
 #include <cstring>
@@ -52,6 +53,7 @@ private:
 
 using KinCabinet = Cabinet<BatchedGasKinetics>;
 using NetCabinet = Cabinet<BatchReactorNet>;
+using TransCabinet = Cabinet<BatchedMixTransport>;
 
 //! handleAllExceptions (clib_utils.h:34-56): -1 for library errors, ERR for anything else.
 template <class R, class F>
@@ -351,6 +353,47 @@ int32_t ctb_kin_getNetProductionRates_ddX_noAlloc(int32_t handle, int64_t nState
 {
     return guard([&] {
         KinCabinet::at(handle)->jacobianNoAlloc(nStates, T, P, Y, ldY, jac, bufLen);
+        return 0;
+    });
+}
+
+// ---- BatchedMixTransport -------------------------------------------------------------------
+
+int32_t ctb_trans_newFromArrays(int32_t nSpecies, const double* molWeights, const double* viscPoly,
+                                const double* condPoly, const double* diffPoly, int32_t device)
+{
+    return guard([&] {
+        return (int32_t) TransCabinet::add(std::make_shared<BatchedMixTransport>(nSpecies, molWeights, viscPoly, condPoly,
+                                                                                 diffPoly, device));
+    });
+}
+
+int32_t ctb_trans_del(int32_t handle)
+{
+    return guard([&] { TransCabinet::del(handle); return 0; });
+}
+
+int32_t ctb_trans_nSpecies(int32_t handle)
+{
+    return guard([&] { return (int32_t) TransCabinet::at(handle)->nSpecies(); });
+}
+
+int32_t ctb_trans_setStream(int32_t handle, void* cudaStream)
+{
+    return guard([&] { TransCabinet::at(handle)->setStream(static_cast<cudaStream_t>(cudaStream)); return 0; });
+}
+
+int32_t ctb_trans_synchronize(int32_t handle)
+{
+    return guard([&] { TransCabinet::at(handle)->synchronize(); return 0; });
+}
+
+int32_t ctb_trans_getMixtureTransport(int32_t handle, int64_t nStates, const double* T, const double* P,
+                                      const double* Y, int64_t ldY, double* viscosity, double* conductivity,
+                                      double* mixDiff, int64_t ldD, int32_t memspace)
+{
+    return guard([&] {
+        TransCabinet::at(handle)->compute(nStates, T, P, Y, ldY, viscosity, conductivity, mixDiff, ldD, memspace);
         return 0;
     });
 }

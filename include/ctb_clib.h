@@ -257,6 +257,29 @@ int32_t ctb_kin_getNetProductionRates_ddX_noAlloc(int32_t handle, int64_t nState
 int32_t ctb_kin_getQuantity(int32_t handle, int32_t quantity, int64_t nStates, const double* T, const double* P,
                             const double* Y, int64_t ldY, double* out, int64_t ld, int32_t memspace);
 
+/* ---- BatchedMixTransport: mixture-averaged transport for N states -------- */
+
+/* newTransport("mixture-averaged") (TransportFactory.cpp, MixTransport::init) for tables: the fitted
+ * temperature polynomials of the reference's GasTransport (non-CK mode, 5 coefficients in ln T), read
+ * through its public getters getViscosityPolynomial / getConductivityPolynomial /
+ * getBinDiffusivityPolynomial (GasTransport.h:107-115): viscPoly, condPoly [K*5]; diffPoly [K(K+1)/2*5],
+ * pairs i <= j row by row (GasTransport.cpp:778-795); molWeights [K]. Returns a handle or -1. */
+int32_t ctb_trans_newFromArrays(int32_t nSpecies, const double* molWeights, const double* viscPoly,
+                                const double* condPoly, const double* diffPoly, int32_t device);
+int32_t ctb_trans_del(int32_t handle);
+int32_t ctb_trans_nSpecies(int32_t handle);
+/* Stream of the device-memory calls, as ctb_kin_setStream. */
+int32_t ctb_trans_setStream(int32_t handle, void* cudaStream);
+int32_t ctb_trans_synchronize(int32_t handle);
+/* trans_viscosity, trans_thermalConductivity and trans_getMixDiffCoeffs (sourcegen/headers/cttrans.yaml:12-16;
+ * GasTransport::viscosity GasTransport.cpp:60-82, MixTransport::thermalConductivity MixTransport.cpp:33-50,
+ * GasTransport::getMixDiffCoeffs GasTransport.cpp:170-201) after setState_TPY, for every state of the batch:
+ * viscosity[n] (Pa s), conductivity[n] (W/m/K), mixDiff[n*ldD + k] (m^2/s). Any of the three output
+ * pointers may be NULL. */
+int32_t ctb_trans_getMixtureTransport(int32_t handle, int64_t nStates, const double* T, const double* P,
+                                      const double* Y, int64_t ldY, double* viscosity, double* conductivity,
+                                      double* mixDiff, int64_t ldD, int32_t memspace);
+
 /* ---- BatchReactorNet: N x { IdealGasConstPressureMoleReactor + ReactorNet } --------------- */
 
 /* ReactorNet(reactor) for nReactors independent reactors sharing the mechanism of a kinetics

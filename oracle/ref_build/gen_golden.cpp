@@ -17,6 +17,7 @@
 #include "cantera/base/global.h"
 #include "cantera/kinetics/Kinetics.h"
 #include "cantera/thermo/ThermoPhase.h"
+#include "cantera/transport/Transport.h"
 #include "cantera/zeroD/IdealGasConstPressureMoleReactor.h"
 #include "cantera/zeroD/IdealGasConstPressureReactor.h"
 #include "cantera/zeroD/IdealGasMoleReactor.h"
@@ -382,18 +383,59 @@ static int runIgnite(shared_ptr<Solution> sol, const std::string& out, size_t N,
     return 0;
 }
 
+// Mixture-averaged transport (MixTransport): the fitted temperature polynomials the
+// reference builds at start-up (public getters of GasTransport.h:107-115) and, for N seeded states, the
+// viscosity, thermal conductivity and mixture-averaged diffusion coefficients it computes from them.
+static int runTrans(const std::string& yaml, const std::string& phase, const std::string& out, size_t N, uint64_t seed)
+{
+    auto sol = newSolution(yaml, phase, "mixture-averaged");
+    auto gas = sol->thermo();
+    auto tr = sol->transport();
+    size_t K = gas->nSpecies();
+    std::vector<double> visc(K * 5), cond(K * 5), diff;
+    for (size_t k = 0; k < K; k++) {
+        tr->getViscosityPolynomial(k, span<double>(&visc[5 * k], 5));
+        tr->getConductivityPolynomial(k, span<double>(&cond[5 * k], 5));
+    }
+    for (size_t i = 0; i < K; i++) {
+        for (size_t j = i; j < K; j++) {
+            double c[5];
+            tr->getBinDiffusivityPolynomial(i, j, span<double>(c, 5));
+            diff.insert(diff.end(), c, c + 5);
+        }
+    }
+    States s = randomStates(N, K, seed);
+    std::vector<double> mu(N), lambda(N), dmix(N * K);
+    for (size_t n = 0; n < N; n++) {
+        gas->setState_TPY(s.T[n], s.P[n], span<const double>(&s.Y[n * K], K));
+        mu[n] = tr->viscosity();
+        lambda[n] = tr->thermalConductivity();
+        tr->getMixDiffCoeffs(span<double>(&dmix[n * K], K));
+    }
+    auto mw = gas->molecularWeights();
+    ArrayFile f;
+    f.add("dims", std::vector<int32_t>{(int32_t) N, (int32_t) K, 0});
+    f.add("mol_weights", std::vector<double>(mw.begin(), mw.end()));
+    f.add("visc_poly", visc); f.add("cond_poly", cond); f.add("diff_poly", diff);
+    f.add("T", s.T); f.add("P", s.P); f.add("Y", s.Y);
+    f.add("viscosity", mu); f.add("conductivity", lambda); f.add("mixdiff", dmix);
+    f.save(out);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 7) {
-        std::cerr << "usage: gen_golden rates|ddx|rhs|rjac|ddxdigest|derivs|ignite yaml phase out N seed [...]\n";
+        std::cerr << "usage: gen_golden rates|ddx|rhs|rjac|ddxdigest|derivs|trans|ignite yaml phase out N seed [...]\n";
         return 2;
     }
     try {
         std::string mode = argv[1], phase = argv[3];
         if (phase == "-") phase = "";
-        auto sol = newSolution(argv[2], phase, "none");
         size_t N = std::stoul(argv[5]);
         uint64_t seed = std::stoull(argv[6]);
+        if (mode == "trans") return runTrans(argv[2], phase, argv[4], N, seed);
+        auto sol = newSolution(argv[2], phase, "none");
         if (mode == "rates") return runRates(sol, argv[4], N, seed);
         if (mode == "ddx") return runDdx(sol, argv[4], N, seed);
         if (mode == "rhs") return runRhs(sol, argv[4], N, seed, argc > 7 ? argv[7] : "IdealGasConstPressureMoleReactor");

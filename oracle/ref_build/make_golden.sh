@@ -59,6 +59,9 @@ gg ddxdigest "$D/h2o2.yaml" ohmech "$G/ddxdigest_h2o2.ctbm" 512 $((SEED+30))
 gg ddxdigest "$D/gri30.yaml" gri30 "$G/ddxdigest_gri30.ctbm" 256 $((SEED+31))
 gg ddxdigest "$D/nDodecane_Reitz.yaml" nDodecane_IG "$G/ddxdigest_nDodecane.ctbm" 64 $((SEED+32))
 gg ddxdigest "$TD/pdep-test.yaml" gas "$G/ddxdigest_pdep-test.ctbm" 64 $((SEED+33))
+# mixture-averaged transport: fitted polynomials + viscosity / conductivity / mixture diffusion coefficients
+gg trans "$D/gri30.yaml" gri30 "$G/trans_gri30.ctbm" 64 20261110
+gg trans "$D/h2o2.yaml" ohmech "$G/trans_h2o2.ctbm" 64 20261111
 gg derivs "$D/h2o2.yaml" ohmech "$G/derivs_h2o2.ctbm" 32 $((SEED+40))
 gg derivs "$D/gri30.yaml" gri30 "$G/derivs_gri30.ctbm" 16 $((SEED+41))
 gg derivs "$D/nDodecane_Reitz.yaml" nDodecane_IG "$G/derivs_nDodecane.ctbm" 8 $((SEED+42))
@@ -73,5 +76,5 @@ for rt in IdealGasMoleReactor IdealGasReactor IdealGasConstPressureReactor; do
     rb ignite "$D/gri30.yaml" gri30 64 $((SEED+53)) "$P" "$D" CH4 2 O2 N2 1000 2000 1 50 1e-3 --reactor $rt --dump "$G/ignite_${rt}_gri30.ctbm" --tign 400
 done
 gzip -9 -f -n "$G"/rates_*.ctbm "$G"/ddx_*.ctbm "$G"/rhs_*.ctbm "$G"/ignite_*.ctbm "$G"/substep_*.ctbm \
-    "$G"/rjac_*.ctbm "$G"/ddxdigest_*.ctbm "$G"/derivs_*.ctbm
+    "$G"/rjac_*.ctbm "$G"/ddxdigest_*.ctbm "$G"/derivs_*.ctbm "$G"/trans_*.ctbm
 ls -la "$G" "$M"
