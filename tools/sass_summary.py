@@ -17,7 +17,10 @@ for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
     if m:
         cur = next(it)
-        cur = re.sub(r"ctb::\(anonymous namespace\)::|\(ctb::[^)]*\)|\(.*\)$", "", cur)[:90]
+        cur = cur.replace("(anonymous namespace)::", "").replace("ctb::", "")
+        cur = re.sub(r"\(.*\)$", "", cur)[:90]
+        while cur in kern:
+            cur += "'"
         kern[cur] = collections.Counter()
         continue
     m = re.match(r"\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
