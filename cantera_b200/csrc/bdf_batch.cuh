@@ -230,35 +230,41 @@ struct BatchBdf {
         // species rows: c.atolS (MoleReactor::updateDefaultTolerances, MoleReactor.cpp:64-76); T, V, m rows: atol
         CTB_FOR_OWN(i) EW(i) = 1.0 / (p.rtol * fabs(ZN(0, i)) + (i < p.sIdx ? p.atol : c.atolS));
     }
-    CTB_HD void predict() {
-        c.tn += c.h;
-        const int q = c.q;
+    //! zn <- Pascal-triangle product (SUB = false: the prediction) or its inverse (SUB = true), for order Q. The
+    //! order is a compile-time constant here (run() dispatches on c.q): Q + 1 loads, Q (Q + 1) / 2 additions in the
+    //! order of cvPredict / cvRestore, Q stores, no predicates.
+    template <int Q, bool SUB>
+    CTB_HD void pascalQ() {
         CTB_FOR_OWN(i) {
-            double z[BDF_QMAX + 1];
+            double z[Q + 1];
 #pragma unroll
-            for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
-            for (int k = 1; k <= q; k++) {
+            for (int j = 0; j <= Q; j++) z[j] = ZN(j, i);
 #pragma unroll
-                for (int j = BDF_QMAX; j >= 1; j--) if (j >= k && j <= q) z[j - 1] += z[j];
+            for (int k = 1; k <= Q; k++) {
+#pragma unroll
+                for (int j = Q; j >= k; j--) z[j - 1] = SUB ? z[j - 1] - z[j] : z[j - 1] + z[j];
             }
 #pragma unroll
-            for (int j = 0; j < BDF_QMAX; j++) if (j < q) ZN(j, i) = z[j];
+            for (int j = 0; j < Q; j++) ZN(j, i) = z[j];
         }
+    }
+    template <bool SUB>
+    CTB_HD void pascal() {
+        switch (c.q) {
+        case 1: pascalQ<1, SUB>(); break;
+        case 2: pascalQ<2, SUB>(); break;
+        case 3: pascalQ<3, SUB>(); break;
+        case 4: pascalQ<4, SUB>(); break;
+        default: pascalQ<5, SUB>(); break;
+        }
+    }
+    CTB_HD void predict() {
+        c.tn += c.h;
+        pascal<false>();
     }
     CTB_HD void restore() {
         c.tn = c.savedT;
-        const int q = c.q;
-        CTB_FOR_OWN(i) {
-            double z[BDF_QMAX + 1];
-#pragma unroll
-            for (int j = 0; j <= BDF_QMAX; j++) z[j] = (j <= q) ? ZN(j, i) : 0.0;
-            for (int k = 1; k <= q; k++) {
-#pragma unroll
-                for (int j = BDF_QMAX; j >= 1; j--) if (j >= k && j <= q) z[j - 1] -= z[j];
-            }
-#pragma unroll
-            for (int j = 0; j < BDF_QMAX; j++) if (j < q) ZN(j, i) = z[j];
-        }
+        pascal<true>();
     }
     CTB_HD void rescale() {
         double factor = c.eta;
@@ -418,6 +424,15 @@ struct BatchBdf {
         c.qwait--;
         if (saveAcor) c.savedTq5 = c.tq[5];
     }
+    //! x^(1/k) for the step-size selection (k = 1 .. 7, x >= 0): square roots where k is a power of two, else
+    //! exp(log(x) / k). The library pow() costs about twice as many instructions and the result only steers
+    //! the step size (cvodes.c cvComputeEtaq*: SUNRpowerR).
+    CTB_HD static double rootK(double x, int k) {
+        if (k == 1) return x;
+        if (k == 2) return sqrt(x);
+        if (k == 4) return sqrt(sqrt(x));
+        return x > 0.0 ? exp(log(x) / k) : 0.0;
+    }
     CTB_HD void setEta() {
         if (c.eta < BDF_THRESH) {
             c.eta = 1.0;
@@ -436,7 +451,7 @@ struct BatchBdf {
             c.eta = 1.0;
             return;
         }
-        const double etaq = 1.0 / (pow(BDF_BIAS2 * dsm, 1.0 / L) + BDF_ADDON);
+        const double etaq = 1.0 / (rootK(BDF_BIAS2 * dsm, L) + BDF_ADDON);
         if (c.qwait != 0) {
             c.eta = etaq;
             c.qprime = q;
@@ -452,17 +467,20 @@ struct BatchBdf {
                 sum += t * t;
             }
             const double ddn = sqrt(g.sum(sum) / n) * c.tq[1];
-            etaqm1 = 1.0 / (pow(BDF_BIAS1 * ddn, 1.0 / q) + BDF_ADDON);
+            etaqm1 = 1.0 / (rootK(BDF_BIAS1 * ddn, q) + BDF_ADDON);
         }
         if (q != BDF_QMAX && c.savedTq5 != 0.0) {
-            const double cquot = (c.tq[5] / c.savedTq5) * pow(c.h / c.tau[2], (double) L);
+            const double hr = c.h / c.tau[2];
+            double hrL = hr; // (h / tau_2)^L, L = 2 .. 6
+            for (int k = 1; k < L; k++) hrL *= hr;
+            const double cquot = (c.tq[5] / c.savedTq5) * hrL;
             double sum = 0.0;
             CTB_FOR_OWN(i) {
                 const double t = (AC(i) - cquot * ZN(BDF_QMAX, i)) * EW(i);
                 sum += t * t;
             }
             const double dup = sqrt(g.sum(sum) / n) * c.tq[3];
-            etaqp1 = 1.0 / (pow(BDF_BIAS3 * dup, 1.0 / (L + 1)) + BDF_ADDON);
+            etaqp1 = 1.0 / (rootK(BDF_BIAS3 * dup, L + 1) + BDF_ADDON);
         }
         const double etam = fmax(etaqm1, fmax(etaq, etaqp1));
         if (etam < BDF_THRESH) {
@@ -966,7 +984,7 @@ struct BatchBdf {
                 }
                 c.etamax = 1.0;
                 if (c.nef <= BDF_MXNEF1) {
-                    c.eta = 1.0 / (pow(BDF_BIAS2 * c.dsm, 1.0 / c.L) + BDF_ADDON);
+                    c.eta = 1.0 / (rootK(BDF_BIAS2 * c.dsm, c.L) + BDF_ADDON);
                     c.eta = fmax(BDF_ETAMIN, c.eta);
                     if (c.nef >= BDF_SMALL_NEF) c.eta = fmin(c.eta, BDF_ETAMXF);
                     if (!(c.eta == c.eta)) c.eta = BDF_ETAMIN;
