@@ -15,6 +15,10 @@
 //
 // with the per-slot integrator memory in HBM. Tens of thousands of reactors are in flight per
 // round, so the chemistry runs at the throughput of the rates kernels.
+// The control kernel works on the slot's controller block where the TMA copy put it (shared memory) instead of
+// copying all of BatchCtl into registers and back on every visit: no spills, ~120 fewer loads / stores per visit
+// (control 2171 -> 2020 ms per 131 072 gri30 reactors). Every lane executes the same scalar updates in lockstep.
+#define CTB_CTL_IN_SMEM 1
 #include "bdf_batch.cuh"
 #include "jac_tile.cuh"
 
