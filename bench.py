@@ -47,6 +47,10 @@ MECH = {
 # dram read+write per gri30 state of the wdot kernel, ncu --set full (profiles/r02_wdot_tile_ncu_details.txt:
 # 461.6 MB read + 408.8 MB written for 1 048 576 states)
 WDOT_TRAFFIC_BYTES_PER_STATE = 830.1
+# the same for the Jacobian tile kernel (profiles/r02_ddx_tile_v2_ncu_details.txt and the .ncu-rep's raw page:
+# 0.53 GB read + 15.94 GB written for 524 288 states; 22 912 B of them algorithmic, the rest is the per-tile
+# coefficient scratch leaving the L2 under the output stream)
+DDX_TRAFFIC_BYTES_PER_STATE = 31408.0
 
 IGNITION = {
     # name: mechanism, fuel, O2 per fuel at phi = 1, species names, T0 range, P range [atm], t_end, default reactors
@@ -495,7 +499,8 @@ def rates_workload(x, args, workload):
         bytes_per = 8 * (K + 2) + 8 * K * K
         gbs = bytes_per * n / (kernel_ms * 1e-3) / 1e9
         peak = hbm or 6541.5
-        rec["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+        rec["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                           "traffic": DDX_TRAFFIC_BYTES_PER_STATE * n if mech == "gri30" else None,
                            "note": "jacKernel writes the dense K x K Jacobian: algorithmic bytes = 8 (K + 2) + 8 K^2 = %d per state "
                                    "(SURVEY.md 8(d)); peak = MEASURED_PEAKS.json hbm_gbs%s" % (bytes_per, "" if hbm else " (absent: fallback 6541.5)"),
                            "kernel_ms": kernel_ms}
