@@ -102,6 +102,46 @@ _PREFIX = {"Y": 1e24, "Z": 1e21, "E": 1e18, "P": 1e15, "T": 1e12, "G": 1e9, "M":
            "c": 1e-2, "m": 1e-3, "u": 1e-6, "n": 1e-9, "p": 1e-12, "f": 1e-15, "a": 1e-18, "z": 1e-21, "y": 1e-24}
 
 
+# dimensions (length, mass, time, quantity, temperature) of the known units, for the convertibility checks of
+# UnitSystem::convert / convertActivationEnergy (Units.cpp:202-211,590-632,676-706)
+_DIMS = {
+    "": (0, 0, 0, 0, 0), "1": (0, 0, 0, 0, 0), "m": (1, 0, 0, 0, 0), "g": (0, 1, 0, 0, 0), "s": (0, 0, 1, 0, 0),
+    "min": (0, 0, 1, 0, 0), "hr": (0, 0, 1, 0, 0), "K": (0, 0, 0, 0, 1), "kmol": (0, 0, 0, 1, 0), "mol": (0, 0, 0, 1, 0),
+    "gmol": (0, 0, 0, 1, 0), "molec": (0, 0, 0, 1, 0), "J": (2, 1, -2, 0, 0), "cal": (2, 1, -2, 0, 0), "erg": (2, 1, -2, 0, 0),
+    "eV": (2, 1, -2, 0, 0), "N": (1, 1, -2, 0, 0), "dyn": (1, 1, -2, 0, 0), "W": (2, 1, -3, 0, 0), "Pa": (-1, 1, -2, 0, 0),
+    "atm": (-1, 1, -2, 0, 0), "bar": (-1, 1, -2, 0, 0), "dyn/cm^2": (-1, 1, -2, 0, 0), "micron": (1, 0, 0, 0, 0),
+    "angstrom": (1, 0, 0, 0, 0), "Å": (1, 0, 0, 0, 0), "L": (3, 0, 0, 0, 0), "l": (3, 0, 0, 0, 0),
+}
+
+
+def unit_dims(name):
+    """(length, mass, time, quantity, temperature) exponents of a unit string."""
+    dims = [0.0] * 5
+    body = re.sub(r"^[+-]?(?:[0-9]+(?:[.][0-9]*)?|[.][0-9]+)", "", name)
+    pos = 0
+    for m in re.finditer(r"[*/]|$", body):
+        group = body[pos:m.start()]
+        sign = -1.0 if pos and body[pos - 1] == "/" else 1.0
+        pos = m.end()
+        exponent = 1.0
+        if "^" in group:
+            group, e = group.split("^", 1)
+            exponent = float(e)
+        unit = group.strip()
+        d = _DIMS[unit] if unit in _DIMS else (_DIMS[unit[1:]] if unit[:1] in _PREFIX and unit[1:] in _DIMS else None)
+        if d is None:
+            raise MechanismError("unknown unit '%s' in unit string '%s'" % (unit, name))
+        for i in range(5):
+            dims[i] += sign * exponent * d[i]
+        if m.start() == len(body):
+            break
+    return tuple(dims)
+
+
+def _same_dims(a, b):
+    return all(abs(x - y) < 1e-9 for x, y in zip(a, b))
+
+
 def unit_factor(name):
     """Conversion factor of a unit string to SI + kmol, with the arithmetic of Units::Units(string)
     (Units.cpp:134-200): group by group, factor *= pow(prefix * unit, +-exponent)."""
@@ -190,6 +230,9 @@ class UnitSystem:
         given dimensions; the multiplication order of convertTo is kept."""
         value, units = _split_unit(v)
         if units:
+            if not _same_dims(unit_dims(units), (length_dim, 0.0, time_dim, quantity_dim, 0.0)):
+                raise MechanismError("incompatible units '%s' for a rate coefficient of dimensions m^%g kmol^%g s^%g"
+                                     % (units, length_dim, quantity_dim, time_dim))
             return value * unit_factor(units) / 1.0
         return (value / 1.0 * math.pow(self.mass, 0.0) * math.pow(self.length, length_dim) * math.pow(self.time, time_dim)
                 * math.pow(self.quantity, quantity_dim) * math.pow(self.pressure, 0.0) * math.pow(self.energy, 0.0))
@@ -200,6 +243,9 @@ class UnitSystem:
         if not units:
             return value * self.activation_energy / GAS_CONSTANT
         cls, f = _energy_class(units), unit_factor(units)
+        want = {"E": (2, 1, -2, -1, 0), "K": (0, 0, 0, 0, 1), "eV": (2, 1, -2, 0, 0)}[cls]
+        if not _same_dims(unit_dims(units), want):
+            raise MechanismError("don't understand units '%s' as an activation energy" % units)
         value *= f if cls == "E" else (GAS_CONSTANT * f if cls == "K" else AVOGADRO * f)
         return value / (GAS_CONSTANT * 1.0)
 
@@ -284,7 +330,10 @@ def _phase_reactions(doc, phase):
     `reactions` section."""
     spec = phase.get("reactions")
     if spec is None:
-        spec = "all" if "reactions" in doc.root else "none"
+        if "reactions" not in doc.root:
+            raise MechanismError("phase '%s' has a kinetics model but the input file has no 'reactions' section "
+                                 "(say 'reactions: none' for a phase without reactions)" % phase.get("name"))
+        spec = "all"
     out = []
 
     def take(section, rule):
@@ -418,6 +467,80 @@ def _recip_or_inf(c):
     return math.inf if abs(c) < SMALL_NUMBER else 1.0 / c
 
 
+def _duplicate_ratio(r1, r2):
+    """Kinetics::checkDuplicateStoich (Kinetics.cpp:251-293): the multiple c with r2 = c r1 (same direction) or
+    r2 = c reversed(r1), 0 when the stoichiometries differ."""
+    keys = set(r1) | set(r2)
+    k1 = min(r1)
+    g1, g2 = (lambda k: r1.get(k, 0.0)), (lambda k: r2.get(k, 0.0))
+    if g1(k1) and g2(k1):
+        ratio = g2(k1) / g1(k1)
+        if not any((g1(k) and not g2(k)) or (not g1(k) and g2(k)) or (g1(k) and abs(g2(k) / g1(k) - ratio) > 1e-8) for k in keys):
+            return ratio
+    if g1(k1) == 0.0 or g2(-k1) == 0.0:
+        return 0.0
+    ratio = g2(-k1) / g1(k1)
+    if any((g1(k) and not g2(-k)) or (not g1(k) and g2(-k)) or (g1(k) and abs(g2(-k) / g1(k) - ratio) > 1e-8) for k in keys):
+        return 0.0
+    return ratio
+
+
+def _check_duplicates(recs, index, names, explicit_tb_rule):
+    """Kinetics::checkDuplicates (Kinetics.cpp:112-249): undeclared duplicate reactions and unmatched `duplicate`
+    flags are errors; `explicit-third-body-duplicates: modify-efficiency` zeroes the explicit collider's
+    efficiency in the generic-M partner (the only way this check changes the tables)."""
+    participants = {}
+    nets = []
+    unmatched = {i for i, r in enumerate(recs) if r["duplicate"]}
+    errors = []
+    for i, R in enumerate(recs):
+        key, net = 0, {}
+        for n, st in R["reac"].items():
+            k = index[n]
+            key += k * (k + 1)
+            net[-1 - k] = net.get(-1 - k, 0.0) - st
+        for n, st in R["prod"].items():
+            k = index[n]
+            key += k * (k + 1)
+            net[1 + k] = net.get(1 + k, 0.0) + st
+        nets.append(net)
+        for m in participants.get(key, []):
+            O = recs[m]
+            if R["duplicate"] and O["duplicate"]:
+                unmatched.discard(i); unmatched.discard(m)
+                continue
+            if R["type"] != O["type"]:
+                continue
+            c = _duplicate_ratio(nets[i], nets[m])
+            if c == 0:
+                continue
+            if c < 0.0 and not R["reversible"] and not O["reversible"]:
+                continue
+            if R["tb"] is not None and O["tb"] is not None:
+                t1, t2 = R["tb"], O["tb"]
+                eff = lambda t, sp: t["effs"].get(sp, t["default"])  # noqa: E731
+                if not any(eff(t1, sp) * eff(t2, sp) != 0.0 for sp in names):
+                    continue
+                if (t1["name"] == "M") != (t2["name"] == "M"):
+                    if explicit_tb_rule == "mark-duplicate":
+                        R["duplicate"] = O["duplicate"] = True
+                        continue
+                    if explicit_tb_rule == "modify-efficiency":
+                        if t1["name"] == "M":
+                            t1["effs"][t2["name"]] = 0.0
+                        else:
+                            t2["effs"][t1["name"]] = 0.0
+                        continue
+                    if explicit_tb_rule == "warn":
+                        continue
+            errors.append("undeclared duplicate reactions: '%s' and '%s'" % (O["eq"], R["eq"]))
+        participants.setdefault(key, []).append(i)
+    for i in sorted(unmatched):
+        errors.append("no duplicate found for the declared duplicate reaction '%s'" % recs[i]["eq"])
+    if errors:
+        raise MechanismError("; ".join(errors))
+
+
 def tables_from_yaml(path, phase="", data_dirs=()):
     """Flat mechanism tables (the keys of a .ctbm file, include/ctb_clib.h ctb_mech_tables) of phase `phase`
     (default: the first phase) of a YAML input file in the reference's format."""
@@ -438,11 +561,24 @@ def tables_from_yaml(path, phase="", data_dirs=()):
     if len(index) != len(names):
         raise MechanismError("duplicate species in phase '%s'" % ph.get("name"))
     K = len(names)
+    # elements (setupPhase, ThermoFactory.cpp): a declared list is closed (species with other elements are an
+    # error, or dropped under skip-undeclared-elements); without a list the elements are added as met
+    declared = "elements" in ph
     elements = [str(e) for e in ph.get("elements", [])]
+    skip_elements = bool(ph.get("skip-undeclared-elements", False))
+    kept = []
     for s in species:
-        for e in sorted(str(x) for x in s.get("composition", {})):
-            if e not in elements:
-                elements.append(e)
+        missing = [e for e in sorted(str(x) for x in s.get("composition", {})) if e not in elements]
+        if missing and declared:
+            if skip_elements:
+                continue
+            raise MechanismError("species '%s' contains the undeclared element(s) %s" % (s["name"], missing))
+        elements += missing
+        kept.append(s)
+    species = kept
+    names = [str(s["name"]) for s in species]
+    index = {n: k for k, n in enumerate(names)}
+    K = len(names)
     molwt, tmid, tmin, tmax, low, high = [], [], [], [], [], []
     p_ref = None
     for s in species:
@@ -475,6 +611,8 @@ def tables_from_yaml(path, phase="", data_dirs=()):
                          "plog_b", "plog_Ea_R", "cheb_nT", "cheb_nP", "cheb_limits", "cheb_coeffs")}
     ptr = {k: [0] for k in ("reac_ptr", "prod_ptr", "tb_ptr", "plog_ptr", "cheb_ptr")}
     equations = []
+    recs = []
+    skip_third_bodies = bool(ph.get("skip-undeclared-third-bodies", False))
     for node, units, skip_undeclared in _phase_reactions(doc, ph):
         eq = str(node["equation"])
         units = units.overlaid(node.get("units"))
@@ -483,6 +621,16 @@ def tables_from_yaml(path, phase="", data_dirs=()):
         third = _detect_third_body(reac, prod, rtype, node, eq)
         orders = {str(k): _num(v) for k, v in (node.get("orders") or {}).items()}
         undeclared = [n for n in list(reac) + list(prod) + list(orders) if n not in index]
+        # a specific collider written as a species ("+ AR") takes part in the parse-time validity check
+        # (Reaction.cpp:932-936); one written "(+AR)" is caught by ThirdBody::checkSpecies (Reaction.cpp:858-882)
+        collider = None if third is None else (third[2:-1].strip() if third.startswith("(+") else third)
+        if collider not in (None, "M") and collider not in index:
+            if not third.startswith("(+"):
+                undeclared.append(collider)
+            elif skip_third_bodies:
+                continue
+            else:
+                raise MechanismError("reaction '%s' has the undeclared third body '%s'" % (eq, collider))
         if undeclared:
             if skip_undeclared:
                 continue
@@ -523,12 +671,11 @@ def tables_from_yaml(path, phase="", data_dirs=()):
         if third is not None:
             flags |= RXN_THIRD_BODY | (RXN_MASS_ACTION if mass_action else 0)
             T["tb_default"].append(tb_default)
-            for k in sorted(index[n] for n in effs if n in index):
-                T["tb_species"].append(k)
-                T["tb_eff"].append(effs[names[k]])
+            unknown = [n for n in effs if n not in index]
+            if unknown and not skip_third_bodies:
+                raise MechanismError("reaction '%s' defines third-body efficiencies for undeclared species %s" % (eq, unknown))
         else:
             T["tb_default"].append(0.0)
-        ptr["tb_ptr"].append(len(T["tb_species"]))
 
         # stoichiometry in the order of the reference's maps (std::map: by name), orders appended (Kinetics.cpp:734-777)
         rk = [index[n] for n in sorted(reac)]
@@ -595,6 +742,12 @@ def tables_from_yaml(path, phase="", data_dirs=()):
         elif kind == "pressure-dependent-Arrhenius":
             code = RATE_PLOG
             entries = [(units.pressure_pa(r["P"]), i, _arrhenius(r, units, conc)) for i, r in enumerate(node["rate-constants"])]
+            # PlogRate::validate (PlogRate.cpp:125-158): the summed rate at every pressure must be positive
+            for P0 in sorted({e[0] for e in entries}):
+                for Tv in (300.0, 500.0, 1000.0, 2000.0, 5000.0, 10000.0):
+                    ksum = sum(pa * math.exp(pb * math.log(Tv) - pe / Tv) for P, _, (pa, pb, pe) in entries if P == P0)
+                    if not ksum > 0:
+                        raise MechanismError("invalid rate coefficient for reaction '%s' at P = %.5g, T = %.1f" % (eq, P0, Tv))
             # std::multimap: by P, stable; PlogRate keeps log(P) and reports exp(log(P)) (PlogRate.cpp:92-123)
             for P, _, (pa, pb, pe) in sorted(entries, key=lambda x: (x[0], x[1])):
                 T["plog_P"].append(math.exp(math.log(P))); T["plog_A"].append(pa); T["plog_b"].append(pb); T["plog_Ea_R"].append(pe)
@@ -617,12 +770,31 @@ def tables_from_yaml(path, phase="", data_dirs=()):
         T["low_A"].append(lA); T["low_b"].append(lb); T["low_Ea_R"].append(lEaR)
         T["falloff_coeffs"] += fc; T["multiplier"].append(1.0)
         T["cheb_nT"].append(nT); T["cheb_nP"].append(nP); T["cheb_limits"] += cheb
+        # Reaction::check / ArrheniusBase::check (Reaction.cpp:137-165, Arrhenius.cpp:113-124)
+        if not node.get("nonreactant-orders", False) and any(n not in reac for n in orders):
+            raise MechanismError("reaction order specified for a non-reactant species in '%s'" % eq)
+        if not node.get("negative-orders", False) and any(v < 0.0 for v in orders.values()):
+            raise MechanismError("negative reaction order in '%s'" % eq)
+        if not node.get("negative-A", False) and (A < 0.0 or lA < 0.0):
+            raise MechanismError("negative pre-exponential factor in '%s' (needs negative-A: true)" % eq)
+        recs.append({"reac": dict(reac), "prod": dict(prod), "reversible": reversible, "duplicate": bool(node.get("duplicate", False)),
+                     "type": (code, flags & (RXN_THIRD_BODY | RXN_MASS_ACTION | RXN_CHEM_ACTIVATED)), "eq": eq,
+                     "tb": None if third is None else {"name": tname, "default": tb_default, "effs": effs}})
         # Reaction::equation (Reaction.cpp:344-387): sides in map order, the collider appended
         collider = "" if third is None else ((" + " + tname) if mass_action else (" (+" + tname + ")"))
 
         def side_string(side):
             return " + ".join(("%g " % side[n] if side[n] != 1.0 else "") + n for n in sorted(side)) + collider
         equations.append(side_string(reac) + (" <=> " if reversible else " => ") + side_string(prod))
+
+    _check_duplicates(recs, index, names, str(ph.get("explicit-third-body-duplicates", "warn")))
+    for rec in recs:  # third-body efficiencies of declared species, by species index (BulkKinetics.cpp:66-84)
+        if rec["tb"] is not None:
+            effs = rec["tb"]["effs"]
+            for k in sorted(index[n] for n in effs if n in index):
+                T["tb_species"].append(k)
+                T["tb_eff"].append(effs[names[k]])
+        ptr["tb_ptr"].append(len(T["tb_species"]))
 
     ints = ("rxn_type", "rxn_flags", "reac_species", "prod_species", "tb_species", "cheb_nT", "cheb_nP")
     out = {"dims": np.array([K, len(equations)], dtype=np.int32), "p_ref": np.array([p_ref if p_ref is not None else ONE_ATM]),

@@ -130,3 +130,100 @@ def test_tables_identical_to_the_reference_extractor(case, fname, phase):
         else:
             assert ours[k].dtype == v.dtype and ours[k].shape == v.shape, k
             assert np.array_equal(ours[k], v), "%s: %d of %d entries differ" % (k, int((ours[k] != v).sum()), v.size)
+
+
+_HEAD = """
+units: {length: cm, quantity: mol, activation-energy: cal/mol}
+phases:
+- name: p
+  thermo: ideal-gas
+  elements: [H, O]
+  species: [A, B, C]
+  kinetics: gas
+  reactions: all
+%s
+species:
+- {name: A, composition: {H: 1}, thermo: {model: NASA7, temperature-ranges: [200.0, 3000.0], data: [[2.5, 0, 0, 0, 0, 0, 0]]}}
+- {name: B, composition: {O: 1}, thermo: {model: NASA7, temperature-ranges: [200.0, 3000.0], data: [[2.5, 0, 0, 0, 0, 0, 0]]}}
+- {name: C, composition: {H: 1, O: 1}, thermo: {model: NASA7, temperature-ranges: [200.0, 3000.0], data: [[3.5, 0, 0, 0, 0, 0, 0]]}}
+reactions:
+%s
+"""
+
+
+def _doc(tmp_path, reactions, phase_extra=""):
+    p = tmp_path / "m.yaml"
+    p.write_text(_HEAD % (phase_extra, reactions))
+    return str(p)
+
+
+@pytest.mark.parametrize("reactions,match", [
+    ("- {equation: A + B <=> C, rate-constant: [1e10, 0, 0]}\n- {equation: A + B <=> C, rate-constant: [2e10, 0, 0]}", "undeclared duplicate"),
+    ("- {equation: A + B <=> C, rate-constant: [1e10, 0, 0]}\n- {equation: C <=> A + B, rate-constant: [2e10, 0, 0]}", "undeclared duplicate"),
+    ("- {equation: A + B <=> C, rate-constant: [1e10, 0, 0], duplicate: true}", "no duplicate found"),
+    ("- {equation: A + B <=> C, rate-constant: [-1e10, 0, 0]}", "negative pre-exponential"),
+    ("- {equation: A + B <=> C, rate-constant: [1e10 cm^6/mol^2/s, 0, 0]}", "incompatible units"),
+    ("- {equation: A + B <=> C, rate-constant: [1e10, 0, 5 m]}", "activation energy"),
+    ("- {equation: A + B => C, rate-constant: [1e10, 0, 0], orders: {C: 1.0}}", "non-reactant"),
+    ("- {equation: A + B <=> C, rate-constant: [1e10, 0, 0], efficiencies: {A: 2.0}}", "no third body"),
+    ("- {equation: A + B + M <=> C + M, rate-constant: [1e10, 0, 0], efficiencies: {ZZ: 2.0}}", "undeclared species"),
+    ("- equation: A + B <=> C\n  type: pressure-dependent-Arrhenius\n  rate-constants:\n  - {P: 1 atm, A: -1e10, b: 0, Ea: 0}\n  - {P: 10 atm, A: 1e10, b: 0, Ea: 0}", "invalid rate coefficient"),
+    ("- {equation: A + B <=> C, type: Blowers-Masel, rate-constant: [1e10, 0, 0, 0]}", "not on the batched path"),
+])
+def test_inputs_the_reference_rejects(tmp_path, reactions, match):
+    """Reaction::check, ArrheniusBase::check, UnitSystem::convert, PlogRate::validate, Kinetics::checkDuplicates."""
+    with pytest.raises(MechanismError, match=match):
+        tables_from_yaml(_doc(tmp_path, reactions), "p")
+
+
+def test_duplicates_and_explicit_third_body_rule(tmp_path):
+    ok = "- {equation: A + B <=> C, rate-constant: [1e10, 0, 0], duplicate: true}\n- {equation: A + B <=> C, rate-constant: [2e10, 0, 1000], duplicate: true}"
+    assert list(tables_from_yaml(_doc(tmp_path, ok), "p")["dims"]) == [3, 2]
+    # irreversible reactions in opposite directions are no duplicates
+    opp = "- {equation: A + B => C, rate-constant: [1e10, 0, 0]}\n- {equation: C => A + B, rate-constant: [2e10, 0, 0]}"
+    assert list(tables_from_yaml(_doc(tmp_path, opp), "p")["dims"]) == [3, 2]
+    # a generic and a specific collider with a common third body: untouched by default, efficiency zeroed on request
+    tb = "- {equation: A + B + M <=> C + M, type: three-body, rate-constant: [1e16, 0, 0], efficiencies: {C: 3.0}}\n" \
+         "- {equation: A + B + C <=> C + C, rate-constant: [2e16, 0, 0]}"
+    t = tables_from_yaml(_doc(tmp_path, tb), "p")
+    assert list(t["tb_species"]) == [2, 2] and list(t["tb_eff"]) == [3.0, 1.0]
+    t = tables_from_yaml(_doc(tmp_path, tb, "  explicit-third-body-duplicates: modify-efficiency"), "p")
+    assert list(t["tb_species"]) == [2, 2] and list(t["tb_eff"]) == [0.0, 1.0]
+
+
+def test_every_ideal_gas_phase_of_the_reference_inputs(tmp_path):
+    """All YAML files of the reference's data and test-data trees: wherever the reference's own loader + extractor
+    (oracle/_ref/ctb_extract) accept an ideal-gas phase, the loader's tables are identical; wherever they refuse
+    it, the loader refuses it too."""
+    import glob
+    import subprocess
+    from cantera_b200.yaml_mech import _load
+    ext = os.path.join(ROOT, "oracle", "_ref", "ctb_extract")
+    D, TD = "/root/reference/data", "/root/reference/test/data"
+    if not (os.path.exists(ext) and os.path.isdir(D)):
+        pytest.skip("needs the reference tree and oracle/_ref/ctb_extract")
+    same = refused = 0
+    for path in sorted(glob.glob(D + "/*.yaml") + glob.glob(TD + "/*.yaml")):
+        try:
+            root = _load(path)
+        except Exception:  # noqa: BLE001  (inputs that are not valid YAML on purpose)
+            continue
+        for ph in (root.get("phases") or []) if isinstance(root, dict) else []:
+            if ph.get("thermo") != "ideal-gas" or ph.get("kinetics") not in ("gas", "bulk"):
+                continue
+            name, out = str(ph["name"]), str(tmp_path / "t.ctbm")
+            r = subprocess.run([ext, path, name, out, D, TD], capture_output=True, text=True, timeout=300)
+            where = "%s:%s" % (os.path.basename(path), name)
+            if r.returncode != 0:
+                with pytest.raises(Exception):
+                    tables_from_yaml(path, name, data_dirs=[D, TD])
+                refused += 1
+                continue
+            ref, ours = read_arrays(out), tables_from_yaml(path, name, data_dirs=[D, TD])
+            for k, v in ref.items():
+                if isinstance(v, str):
+                    assert ours[k] == v, (where, k)
+                else:
+                    assert ours[k].shape == v.shape and np.array_equal(ours[k], v, equal_nan=True), (where, k)
+            same += 1
+    assert same >= 60 and refused >= 20
