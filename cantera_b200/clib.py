@@ -110,6 +110,8 @@ BRIDGE_SIGNATURES = {
     "ctb_kin_new": (_i32, [_i32, C.c_char_p, C.c_char_p, _i32]),
     "ctb_kin_newFromSolution": (_i32, [C.c_void_p, _i32]),
     "ctb_addDataDirectory": (_i32, [C.c_char_p]),
+    "ctb_trans_new": (_i32, [C.c_char_p, C.c_char_p, _i32]),
+    "ctb_trans_newFromSolution": (_i32, [C.c_void_p, _i32]),
 }
 _BRIDGE = None
 

@@ -10,8 +10,11 @@
 
 #include "cantera/base/Solution.h"
 #include "cantera/base/global.h"
+#include "cantera/thermo/ThermoPhase.h"
+#include "cantera/transport/Transport.h"
 
 #include <string>
+#include <vector>
 
 namespace {
 
@@ -64,6 +67,47 @@ int32_t ctb_kin_new(int32_t solHandle, const char* yaml, const char* phase, int3
         if (!yaml) throw Cantera::CanteraError("ctb_kin_new", "null file name");
         auto sol = Cantera::newSolution(yaml, phase ? phase : "", "none");
         return ctb_kin_newFromSolution(sol.get(), device);
+    });
+}
+
+int32_t ctb_trans_newFromSolution(void* solution, int32_t device)
+{
+    return bridged([&] {
+        if (!solution) throw Cantera::CanteraError("ctb_trans_newFromSolution", "null Solution");
+        auto& sol = *static_cast<Cantera::Solution*>(solution);
+        auto thermo = sol.thermo();
+        auto tr = sol.transport();
+        if (!thermo || !tr) throw Cantera::CanteraError("ctb_trans_newFromSolution", "Solution has no thermo / transport");
+        if (tr->transportModel() != "mixture-averaged") {
+            throw Cantera::CanteraError("ctb_trans_newFromSolution", "only the mixture-averaged model (non-CK fits) is on the "
+                                        "batched path; got '{}'", tr->transportModel());
+        }
+        // the fitted temperature polynomials, through the public getters (GasTransport.h:107-115)
+        const size_t K = thermo->nSpecies();
+        std::vector<double> visc(5 * K), cond(5 * K), diff;
+        for (size_t k = 0; k < K; k++) {
+            tr->getViscosityPolynomial(k, Cantera::span<double>(&visc[5 * k], 5));
+            tr->getConductivityPolynomial(k, Cantera::span<double>(&cond[5 * k], 5));
+        }
+        for (size_t i = 0; i < K; i++) {
+            for (size_t j = i; j < K; j++) {
+                double c[5];
+                tr->getBinDiffusivityPolynomial(i, j, Cantera::span<double>(c, 5));
+                diff.insert(diff.end(), c, c + 5);
+            }
+        }
+        auto mw = thermo->molecularWeights();
+        std::vector<double> w(mw.begin(), mw.end());
+        return ctb_trans_newFromArrays((int32_t) K, w.data(), visc.data(), cond.data(), diff.data(), device);
+    });
+}
+
+int32_t ctb_trans_new(const char* yaml, const char* phase, int32_t device)
+{
+    return bridged([&] {
+        if (!yaml) throw Cantera::CanteraError("ctb_trans_new", "null file name");
+        auto sol = Cantera::newSolution(yaml, phase ? phase : "", "mixture-averaged");
+        return ctb_trans_newFromSolution(sol.get(), device);
     });
 }
 

@@ -45,6 +45,22 @@ class BatchedMixTransport:
         self.n_species = K
         self.device = device
 
+    @classmethod
+    def from_yaml(cls, yaml, phase="", device=0, data_dirs=()):
+        """newSolution(yaml, phase, "mixture-averaged") by the reference itself, in this process, through the optional
+        bridge libctb_cantera.so (include/ctb_cantera.h: ctb_trans_new)."""
+        b = clib.bridge()
+        if b is None:
+            raise clib.CtbError("libctb_cantera.so (the reference bridge) is not built; use a transport table file")
+        for d in data_dirs:
+            clib.check(b.ctb_addDataDirectory(str(d).encode()))
+        self = cls.__new__(cls)
+        self._lib = clib.lib()
+        self._h = clib.check(b.ctb_trans_new(str(yaml).encode(), phase.encode(), device))
+        self.n_species = clib.check(self._lib.ctb_trans_nSpecies(self._h))
+        self.device = device
+        return self
+
     def close(self):
         if getattr(self, "_h", None) is not None:
             self._lib.ctb_trans_del(self._h)

@@ -20,6 +20,13 @@ extern "C" {
 int32_t ctb_kin_new(int32_t solHandle, const char* yaml, const char* phase, int32_t device);
 /* The same from a live reference object: solution = Cantera::Solution* (C++ callers of the bridge). */
 int32_t ctb_kin_newFromSolution(void* solution, int32_t device);
+/* newSolution(yaml, phase, "mixture-averaged") in process; the fitted temperature polynomials of its transport
+ * object (GasTransport::getViscosityPolynomial / getConductivityPolynomial / getBinDiffusivityPolynomial,
+ * GasTransport.h:107-115) and the molecular weights go to ctb_trans_newFromArrays. Returns a transport handle of
+ * libctb.so (ctb_trans_*), or -1 with the message set. */
+int32_t ctb_trans_new(const char* yaml, const char* phase, int32_t device);
+/* The same from a live Cantera::Solution* whose transport model is "mixture-averaged". */
+int32_t ctb_trans_newFromSolution(void* solution, int32_t device);
 /* Directory searched for mechanism files (Cantera::addDataDirectory). */
 int32_t ctb_addDataDirectory(const char* dir);
 

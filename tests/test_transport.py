@@ -44,6 +44,41 @@ def test_product_tables_hold_the_reference_polynomials(case):
         assert np.array_equal(t[k], g[k]), k
 
 
+def test_bridge_extracts_transport_in_process():
+    """ctb_trans_new (include/ctb_cantera.h): newSolution(..., "mixture-averaged") by the reference in this process,
+    polynomials through its public getters, then ctb_trans_newFromArrays. Without a GPU the call must get as far
+    as the device check of the constructor (the extraction itself has then succeeded); with one it yields a
+    handle whose results equal those of the table file."""
+    import os
+    from conftest import ROOT
+    from cantera_b200 import clib
+    b = clib.bridge()
+    ref_dir = os.path.join(ROOT, "oracle", "_ref", "data")
+    if b is None or not os.path.exists(os.path.join(ref_dir, "h2o2.yaml")):
+        pytest.skip("libctb_cantera.so / the reference's data files are not on this machine")
+    clib.check(b.ctb_addDataDirectory(ref_dir.encode()))
+    h = b.ctb_trans_new(os.path.join(ref_dir, "h2o2.yaml").encode(), b"ohmech", 0)
+    if h == -1:
+        assert "no usable CUDA device" in clib.last_error()
+        return
+    from cantera_b200.transport import BatchedMixTransport
+    g = golden("trans", "h2o2")
+    N, K, _ = g["dims"]
+    assert clib.check(clib.lib().ctb_trans_nSpecies(h)) == K
+    clib.check(clib.lib().ctb_trans_del(h))
+    tr, tr2 = BatchedMixTransport("h2o2"), BatchedMixTransport.from_yaml(os.path.join(ref_dir, "h2o2.yaml"), "ohmech")
+    a = tr.mixture_transport(g["T"], g["P"], g["Y"].reshape(N, K))
+    c = tr2.mixture_transport(g["T"], g["P"], g["Y"].reshape(N, K))
+    assert all(np.array_equal(x, y) for x, y in zip(a, c))
+    # a phase without the mixture-averaged model is refused with the reference's message
+    assert b.ctb_trans_new(os.path.join(ref_dir, "no-such-file.yaml").encode(), b"", 0) == -1
+
+
+@pytest.mark.gpu
+def test_gpu_bridge_transport_matches_table_file():
+    test_bridge_extracts_transport_in_process()
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", CASES)
 def test_gpu_mixture_transport(case):
