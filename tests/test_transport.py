@@ -69,7 +69,9 @@ def test_bridge_extracts_transport_in_process():
     tr, tr2 = BatchedMixTransport("h2o2"), BatchedMixTransport.from_yaml(os.path.join(ref_dir, "h2o2.yaml"), "ohmech")
     a = tr.mixture_transport(g["T"], g["P"], g["Y"].reshape(N, K))
     c = tr2.mixture_transport(g["T"], g["P"], g["Y"].reshape(N, K))
-    assert all(np.array_equal(x, y) for x, y in zip(a, c))
+    # the fits are recomputed by the reference on THIS host (libm variants may differ from the machine that wrote
+    # the table file in the last bits), so not bit for bit
+    assert all(np.allclose(x, y, rtol=1e-9, atol=0.0) for x, y in zip(a, c))
     # a phase without the mixture-averaged model is refused with the reference's message
     assert b.ctb_trans_new(os.path.join(ref_dir, "no-such-file.yaml").encode(), b"", 0) == -1
 
